@@ -1,0 +1,182 @@
+/* =============================================================================
+ * include/charon_gpu.h — C-ABI of libcharon_gpu.so (B200 / sm_100a)
+ *
+ * The reference (rmcolq/charon) has no plugin/FFI seam: its hot path is the body of
+ * the OpenMP loop in dehost_reads / classify_reads.  This header is the seam a
+ * maintainer would cut there (see INTEGRATION.md for the call-site patch).  Each
+ * entry point cites the reference code it replaces (paths relative to the reference
+ * root).  Plain pointers and sizes only; no C++/torch types cross the boundary.
+ *
+ * Conventions
+ *   - every function returns 0 on success, a negative cg_status on error;
+ *     cg_last_error(h) (or cg_last_error(NULL) for cg_create failures) returns a
+ *     NUL-terminated description valid until the next call on the same thread.
+ *   - one handle per GPU; calls on one handle must be serialised by the caller,
+ *     different handles may be driven from different host threads.
+ *   - host buffers are caller-owned (pinned memory recommended); device memory and
+ *     streams are library-owned.  Outputs are indexed by input read position.
+ *   - there is NO CPU fallback: without a usable sm_100 device cg_create fails.
+ * ============================================================================= */
+#ifndef CHARON_GPU_H
+#define CHARON_GPU_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct cg_handle cg_handle;
+
+enum cg_status {
+    CG_OK = 0,
+    CG_ERR_ARG = -1,      /* invalid argument / unsupported parameter (k > 26, bins > 256, ...) */
+    CG_ERR_CUDA = -2,     /* CUDA runtime error (message has the cudaError string) */
+    CG_ERR_NO_DEVICE = -3,/* no CUDA device / not an sm_100 part: the product has no CPU path */
+    CG_ERR_FORMAT = -4,   /* index payload fails a structural invariant */
+    CG_ERR_STATE = -5,    /* call order violated (e.g. eval before set_model) */
+    CG_ERR_NOMEM = -6     /* filter does not fit the given memory budget in replicated mode */
+};
+
+/* How the Interleaved Bloom Filter payload is handed over (include/index.hpp:26,122-138). */
+enum cg_filter_format {
+    CG_FILTER_PLAIN_ROWS = 0, /* host bit matrix, row-major, bin_words u64 per row (seqan3 uncompressed layout) */
+    CG_FILTER_SD_VECTOR = 1   /* sdsl::sd_vector parts exactly as stored in the .idx file; decoded on the GPU */
+};
+
+/* Index description produced by the host loader (replaces Index + ibf_ members,
+ * include/index.hpp:21-26 ; IBF header fields as serialised by seqan3). */
+typedef struct cg_index_desc {
+    uint8_t kmer_size;       /* include/index.hpp:22 */
+    uint8_t window_size;     /* include/index.hpp:21 */
+    uint64_t bins, technical_bins, bin_size, hash_shift, bin_words, hash_funs;
+    int32_t filter_format;   /* enum cg_filter_format */
+    const uint64_t *rows;    /* PLAIN_ROWS: bin_size * bin_words words */
+    const uint64_t *sd_low;  /* SD_VECTOR: m_low words */
+    uint64_t sd_low_bits;
+    const uint64_t *sd_high; /* SD_VECTOR: m_high words */
+    uint64_t sd_high_bits;
+    uint8_t sd_wl;
+    uint16_t ncat;             /* InputSummary::num_categories(), include/input_summary.hpp:35-37 */
+    const uint8_t *bin_to_cat; /* bins entries: category index of each bin (input_summary.hpp:19-20,39-45) */
+} cg_index_desc;
+
+enum cg_dist { CG_DIST_KDE = 0, CG_DIST_BETA = 1, CG_DIST_GAMMA = 2 };
+
+/* One Model (include/classify_stats.hpp:261-393).  For KDE the datasets are given in the exact
+ * order the reference sums them (KDEParams ctor sorts ascending, fit() keeps training order). */
+typedef struct cg_category_model {
+    int32_t dist;                 /* enum cg_dist */
+    const float *pos; uint32_t npos; float h_pos;   /* k_pos: dataset, bandwidth (:270) */
+    const float *neg; uint32_t nneg; float h_neg;   /* k_neg (:271) */
+    float beta_pos[2], beta_neg[2];                 /* alpha, beta (:268-269) */
+    float gamma_pos[3], gamma_neg[3];               /* shape, loc, scale (:266-267) */
+} cg_category_model;
+
+/* StatsModel thresholds (include/classify_stats.hpp:399-409). */
+typedef struct cg_thresholds {
+    float min_quality;
+    uint32_t min_length;
+    float min_compression;
+    int8_t confidence_threshold;
+    float confidence_probability_threshold;
+    uint8_t min_hits;
+    float host_unique_prop_lo_threshold;
+    float min_proportion_difference;
+    float min_prob_difference;
+    uint8_t host_index;           /* InputSummary::host_category_index(), input_summary.hpp:47-55 */
+} cg_thresholds;
+
+enum cg_mode { CG_MODE_DEHOST = 0 /* ReadEntry::call_host */, CG_MODE_CLASSIFY = 1 /* ReadEntry::call_category */ };
+
+/* A batch of reads.  bases = concatenated raw ASCII sequence characters (any case, IUPAC);
+ * segment s is bases[seg_off[s] .. seg_off[s+1]); read r owns segments read_seg[r] .. read_seg[r+1]
+ * (1 for single-end, 2 for paired: src/dehost_main.cpp:458-465).  read_seg may be NULL: one
+ * segment per read. */
+typedef struct cg_batch {
+    const char *bases;
+    const uint64_t *seg_off;   /* n_segs + 1 entries */
+    const uint32_t *read_seg;  /* n_reads + 1 entries or NULL */
+    uint32_t n_reads;
+    uint32_t n_segs;
+} cg_batch;
+
+/* Per-read integer outputs of ReadEntry::get_counts (include/read_entry.hpp:92-138). */
+typedef struct cg_counts_out {
+    uint32_t *num_hashes;      /* [n_reads]            read_entry.hpp:86-90 */
+    uint32_t *counts;          /* [n_reads * ncat]     read_entry.hpp:102-114 */
+    uint32_t *unique_counts;   /* [n_reads * ncat]     read_entry.hpp:122-136 */
+} cg_counts_out;
+
+/* Per-read host-side scalars feeding the call logic (src/dehost_main.cpp:345-363). */
+typedef struct cg_read_scalars {
+    const float *mean_quality;
+    const float *compression;
+    const uint32_t *length;
+} cg_read_scalars;
+
+/* Per-read outputs of apply_model + call_host / call_category (read_entry.hpp:157-291). */
+typedef struct cg_calls_out {
+    double *probabilities;     /* [n_reads * ncat] */
+    uint8_t *call;             /* [n_reads], 255 = unclassified */
+    uint8_t *confidence;       /* [n_reads] */
+} cg_calls_out;
+
+/* ---- lifetime -------------------------------------------------------------------------- */
+/* Replaces load_index' in-memory IBF + Index::agent() (src/load_index.cpp:8-15, include/index.hpp:110-112):
+ * uploads the filter, re-lays it out column-compacted in HBM.  mem_budget_bytes = 0: whole device. */
+int cg_create(int device, const cg_index_desc *desc, size_t mem_budget_bytes, cg_handle **out);
+void cg_destroy(cg_handle *h);
+const char *cg_last_error(const cg_handle *h);
+/* Use an externally created cudaStream_t (e.g. torch's current stream) for all work; NULL = own stream. */
+int cg_set_stream(cg_handle *h, void *cuda_stream);
+int cg_sync(cg_handle *h);
+
+/* Replaces StatsModel construction / Model::train results (include/classify_stats.hpp:428-473). */
+int cg_set_model(cg_handle *h, const cg_category_model *per_category, const cg_thresholds *thr, int mode);
+
+/* ---- hot path, host buffers in / host buffers out -------------------------------------- */
+/* loop body src/dehost_main.cpp:366-373: minimiser_hash -> bulk_contains -> update_entry -> post_process */
+int cg_count_batch(cg_handle *h, const cg_batch *batch, const cg_counts_out *out);
+/* Result::classify_read -> ReadEntry::dehost / classify (include/result.hpp:97-102) on counts already known
+ * (needed when the host trains the model between counting and calling, result.hpp:136-152). */
+int cg_eval_batch(cg_handle *h, uint32_t n_reads, const uint32_t *num_hashes, const uint32_t *counts,
+                  const uint32_t *unique_counts, const cg_read_scalars *scalars, const cg_calls_out *out);
+/* count + eval fused (model fixed up front: the default no---extract invocation). */
+int cg_classify_batch(cg_handle *h, const cg_batch *batch, const cg_read_scalars *scalars,
+                      const cg_counts_out *counts_out, const cg_calls_out *calls_out);
+
+/* ---- staged (device-resident) variant used to time the kernels without PCIe -------------- */
+int cg_stage_batch(cg_handle *h, const cg_batch *batch, const cg_read_scalars *scalars);  /* H2D only */
+int cg_run_staged(cg_handle *h, int with_eval);                                            /* kernels only, async */
+int cg_fetch_staged(cg_handle *h, const cg_counts_out *counts_out, const cg_calls_out *calls_out); /* D2H + sync */
+
+/* ---- introspection ----------------------------------------------------------------------- */
+typedef struct cg_info {
+    uint64_t filter_bytes;        /* compacted filter size in HBM */
+    uint32_t row_bits;            /* compacted row width (power of two >= bins) */
+    uint32_t single_pass;         /* 1 when every category owns exactly one bin (best bin static) */
+    uint32_t sm_count;
+    uint32_t count_grid, count_block, count_smem_bytes;
+    uint64_t last_minimisers;     /* sum of num_hashes over the last counted batch */
+    uint64_t last_bases;
+    uint32_t last_kernel_launches;
+    float last_count_kernel_ms;   /* CUDA-event time of the count kernel of the last batch */
+    float last_eval_kernel_ms;
+    float last_h2d_ms, last_d2h_ms;
+} cg_info;
+int cg_get_info(cg_handle *h, cg_info *out);
+
+/* Test hooks (stage-level parity): emitted minimiser values of one sequence in emission order is not
+ * defined on the GPU (compaction is unordered) — values are returned sorted ascending. */
+int cg_debug_minimisers(cg_handle *h, const char *bases, uint64_t len, uint64_t *out, uint64_t cap, uint64_t *n_out);
+/* bulk_contains for n hash values: masks[n * bin_words] in the seqan3 binning_bitvector word layout. */
+int cg_debug_query(cg_handle *h, const uint64_t *values, uint64_t n, uint64_t *masks);
+/* Copy the compacted filter back expanded to the plain row layout (bin_size * bin_words words). */
+int cg_debug_dump_filter(cg_handle *h, uint64_t *rows_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CHARON_GPU_H */
