@@ -1,0 +1,289 @@
+"""ctypes binding of libcharon_gpu.so (include/charon_gpu.h) and a thin host-side mirror of the reference's
+classification objects for Python callers (tests, bench).
+
+The product path has NO CPU fallback: if the CUDA library is missing or no B200 is visible, construction raises.
+Nothing in this package imports the oracle.
+"""
+import ctypes as C
+import os
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libcharon_gpu.so")
+
+u8, u16, u32, u64, i32, f32, f64, vp = C.c_uint8, C.c_uint16, C.c_uint32, C.c_uint64, C.c_int32, C.c_float, C.c_double, C.c_void_p
+
+
+class IndexDesc(C.Structure):
+    _fields_ = [("kmer_size", u8), ("window_size", u8), ("bins", u64), ("technical_bins", u64), ("bin_size", u64), ("hash_shift", u64),
+                ("bin_words", u64), ("hash_funs", u64), ("filter_format", i32), ("rows", vp), ("sd_low", vp), ("sd_low_bits", u64),
+                ("sd_high", vp), ("sd_high_bits", u64), ("sd_wl", u8), ("ncat", u16), ("bin_to_cat", vp)]
+
+
+class CategoryModel(C.Structure):
+    _fields_ = [("dist", i32), ("pos", vp), ("npos", u32), ("h_pos", f32), ("neg", vp), ("nneg", u32), ("h_neg", f32),
+                ("beta_pos", f32 * 2), ("beta_neg", f32 * 2), ("gamma_pos", f32 * 3), ("gamma_neg", f32 * 3)]
+
+
+class Thresholds(C.Structure):
+    _fields_ = [("min_quality", f32), ("min_length", u32), ("min_compression", f32), ("confidence_threshold", C.c_int8),
+                ("confidence_probability_threshold", f32), ("min_hits", u8), ("host_unique_prop_lo_threshold", f32),
+                ("min_proportion_difference", f32), ("min_prob_difference", f32), ("host_index", u8)]
+
+
+class Batch(C.Structure):
+    _fields_ = [("bases", vp), ("seg_off", vp), ("read_seg", vp), ("n_reads", u32), ("n_segs", u32)]
+
+
+class CountsOut(C.Structure):
+    _fields_ = [("num_hashes", vp), ("counts", vp), ("unique_counts", vp)]
+
+
+class ReadScalars(C.Structure):
+    _fields_ = [("mean_quality", vp), ("compression", vp), ("length", vp)]
+
+
+class CallsOut(C.Structure):
+    _fields_ = [("probabilities", vp), ("call", vp), ("confidence", vp)]
+
+
+class Info(C.Structure):
+    _fields_ = [("filter_bytes", u64), ("row_bits", u32), ("single_pass", u32), ("sm_count", u32), ("count_grid", u32),
+                ("count_block", u32), ("count_smem_bytes", u32), ("last_minimisers", u64), ("last_bases", u64),
+                ("last_kernel_launches", u32), ("last_count_kernel_ms", f32), ("last_eval_kernel_ms", f32), ("last_h2d_ms", f32),
+                ("last_d2h_ms", f32)]
+
+
+EXPORTS = ["cg_create", "cg_destroy", "cg_last_error", "cg_set_stream", "cg_sync", "cg_set_model", "cg_count_batch", "cg_eval_batch",
+           "cg_classify_batch", "cg_stage_batch", "cg_run_staged", "cg_fetch_staged", "cg_get_info", "cg_debug_minimisers",
+           "cg_debug_query", "cg_debug_dump_filter"]
+
+_lib = None
+
+
+def load_library():
+    """dlopen libcharon_gpu.so; raises (never falls back) when it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(f"{LIB_PATH} is missing: build it with `make -C charon_b200/csrc` (or __graft_entry__.build()); "
+                           "charon_b200 has no CPU fallback")
+    L = C.CDLL(LIB_PATH)
+    P = C.POINTER
+    L.cg_create.argtypes = [i32, P(IndexDesc), C.c_size_t, P(vp)]
+    L.cg_destroy.argtypes = [vp]; L.cg_destroy.restype = None
+    L.cg_last_error.argtypes = [vp]; L.cg_last_error.restype = C.c_char_p
+    L.cg_set_stream.argtypes = [vp, vp]
+    L.cg_sync.argtypes = [vp]
+    L.cg_set_model.argtypes = [vp, P(CategoryModel), P(Thresholds), i32]
+    L.cg_count_batch.argtypes = [vp, P(Batch), P(CountsOut)]
+    L.cg_eval_batch.argtypes = [vp, u32, vp, vp, vp, P(ReadScalars), P(CallsOut)]
+    L.cg_classify_batch.argtypes = [vp, P(Batch), P(ReadScalars), P(CountsOut), P(CallsOut)]
+    L.cg_stage_batch.argtypes = [vp, P(Batch), P(ReadScalars)]
+    L.cg_run_staged.argtypes = [vp, i32]
+    L.cg_fetch_staged.argtypes = [vp, P(CountsOut), P(CallsOut)]
+    L.cg_get_info.argtypes = [vp, P(Info)]
+    L.cg_debug_minimisers.argtypes = [vp, vp, u64, vp, u64, P(u64)]
+    L.cg_debug_query.argtypes = [vp, vp, u64, vp]
+    L.cg_debug_dump_filter.argtypes = [vp, vp]
+    _lib = L
+    return L
+
+
+class CharonGpuError(RuntimeError):
+    pass
+
+
+def _ptr(a):
+    return a.ctypes.data if a is not None else None
+
+
+class DehostOptions:
+    """Thresholds of DehostArguments (reference include/dehost_arguments.hpp:22-43)."""
+    mode = 0
+
+    def __init__(self, **kw):
+        self.dist = "kde"; self.min_quality = 15.0; self.min_length = 140; self.min_compression = 0.0
+        self.confidence_threshold = 7; self.confidence_probability_threshold = 0.0; self.host_unique_prop_lo_threshold = 0.05
+        self.min_proportion_difference = 0.04; self.min_prob_difference = 0.0; self.min_hits = 0
+        self.__dict__.update(kw)
+
+
+class ClassifyOptions(DehostOptions):
+    """Thresholds of ClassifyArguments (reference include/classify_arguments.hpp:16-39)."""
+    mode = 1
+
+    def __init__(self, **kw):
+        super().__init__()
+        self.dist = "beta"; self.min_quality = 10.0; self.min_compression = 0.15; self.confidence_threshold = 2
+        self.min_proportion_difference = 0.0
+        self.__dict__.update(kw)
+
+
+class GpuClassifier:
+    """One handle = one GPU holding the compacted filter.  Mirrors what Index::agent() + Result give the
+    reference's loop (src/dehost_main.cpp:321,331): `count_batch`, `classify_batch`."""
+
+    def __init__(self, *, k, w, bins, bin_size, hash_funs, bin_to_cat, ncat, rows=None, sd=None, device=0, mem_budget=0):
+        L = load_library()
+        self._L = L
+        self.k, self.w, self.bins, self.bin_size, self.ncat = k, w, bins, bin_size, ncat
+        self.bin_words = (bins + 63) // 64
+        d = IndexDesc()
+        d.kmer_size, d.window_size, d.bins, d.bin_words = k, w, bins, self.bin_words
+        d.technical_bins, d.bin_size, d.hash_funs = self.bin_words * 64, bin_size, hash_funs
+        d.hash_shift = 64 - int(bin_size).bit_length()
+        self._keep = []
+        if rows is not None:
+            rows = np.ascontiguousarray(rows, dtype=np.uint64)
+            assert rows.size == bin_size * self.bin_words
+            d.filter_format, d.rows = 0, rows.ctypes.data
+            self._keep.append(rows)
+        else:
+            low, low_bits, high, high_bits, wl = sd
+            low = np.ascontiguousarray(low, dtype=np.uint64); high = np.ascontiguousarray(high, dtype=np.uint64)
+            d.filter_format, d.sd_low, d.sd_low_bits, d.sd_high, d.sd_high_bits, d.sd_wl = 1, low.ctypes.data, low_bits, high.ctypes.data, high_bits, wl
+            self._keep += [low, high]
+        b2c = np.ascontiguousarray(bin_to_cat, dtype=np.uint8)
+        d.ncat, d.bin_to_cat = ncat, b2c.ctypes.data
+        self._keep.append(b2c)
+        h = vp()
+        rc = L.cg_create(device, C.byref(d), mem_budget, C.byref(h))
+        if rc != 0:
+            raise CharonGpuError(f"cg_create failed ({rc}): {L.cg_last_error(None).decode()}")
+        self._h = h
+        self._model_keep = None
+
+    # ---- plumbing -----------------------------------------------------------------------------------------
+    def _check(self, rc, what):
+        if rc != 0:
+            raise CharonGpuError(f"{what} failed ({rc}): {self._L.cg_last_error(self._h).decode()}")
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.cg_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def info(self) -> Info:
+        i = Info()
+        self._check(self._L.cg_get_info(self._h, C.byref(i)), "cg_get_info")
+        return i
+
+    def set_stream(self, cuda_stream_ptr):
+        self._check(self._L.cg_set_stream(self._h, cuda_stream_ptr), "cg_set_stream")
+
+    def sync(self):
+        self._check(self._L.cg_sync(self._h), "cg_sync")
+
+    # ---- model ----------------------------------------------------------------------------------------------
+    def set_model(self, opts, host_index=0, kde_pos=None, kde_neg=None, h_pos=0.1, h_neg=0.001):
+        """opts: DehostOptions / ClassifyOptions.  kde_pos/kde_neg: datasets in summation order (default: the
+        reference's built-in data, sorted ascending as KDEParams' ctor does, classify_stats.hpp:214-218)."""
+        from .kde_defaults import default_pos_sorted, default_neg_sorted
+        pos = np.ascontiguousarray(kde_pos if kde_pos is not None else default_pos_sorted(), dtype=np.float32)
+        neg = np.ascontiguousarray(kde_neg if kde_neg is not None else default_neg_sorted(), dtype=np.float32)
+        dist = {"kde": 0, "beta": 1, "gamma": 2}[opts.dist]
+        arr = (CategoryModel * self.ncat)()
+        for m in arr:
+            m.dist = dist
+            m.pos, m.npos, m.h_pos = pos.ctypes.data, len(pos), h_pos
+            m.neg, m.nneg, m.h_neg = neg.ctypes.data, len(neg), h_neg
+            m.beta_pos[:] = [6, 4]; m.beta_neg[:] = [6, 40]                      # classify_stats.hpp:268-269
+            m.gamma_pos[:] = [25, 0, 0.02]; m.gamma_neg[:] = [10, 0, 0.005]      # classify_stats.hpp:266-267
+        t = Thresholds(opts.min_quality, opts.min_length, opts.min_compression, opts.confidence_threshold,
+                       opts.confidence_probability_threshold, opts.min_hits, opts.host_unique_prop_lo_threshold,
+                       opts.min_proportion_difference, opts.min_prob_difference, host_index)
+        self._model_keep = (pos, neg)
+        self._check(self._L.cg_set_model(self._h, arr, C.byref(t), opts.mode), "cg_set_model")
+
+    # ---- batches --------------------------------------------------------------------------------------------
+    def _batch(self, bases, seg_off, read_seg):
+        bases = np.ascontiguousarray(bases, dtype=np.uint8)
+        seg_off = np.ascontiguousarray(seg_off, dtype=np.uint64)
+        rs = np.ascontiguousarray(read_seg, dtype=np.uint32) if read_seg is not None else None
+        n_segs = len(seg_off) - 1
+        n_reads = len(rs) - 1 if rs is not None else n_segs
+        b = Batch(bases.ctypes.data, seg_off.ctypes.data, _ptr(rs), n_reads, n_segs)
+        return b, (bases, seg_off, rs), n_reads
+
+    def _outs(self, n, with_calls):
+        res = dict(num_hashes=np.zeros(n, np.uint32), counts=np.zeros((n, self.ncat), np.uint32), unique_counts=np.zeros((n, self.ncat), np.uint32))
+        co = CountsOut(res["num_hashes"].ctypes.data, res["counts"].ctypes.data, res["unique_counts"].ctypes.data)
+        ca = None
+        if with_calls:
+            res.update(prob=np.zeros((n, self.ncat), np.float64), call=np.zeros(n, np.uint8), confidence=np.zeros(n, np.uint8))
+            ca = CallsOut(res["prob"].ctypes.data, res["call"].ctypes.data, res["confidence"].ctypes.data)
+        return res, co, ca
+
+    @staticmethod
+    def _scalars(n, mean_q, compression, length):
+        mq = np.ascontiguousarray(mean_q, dtype=np.float32); cr = np.ascontiguousarray(compression, dtype=np.float32)
+        ln = np.ascontiguousarray(length, dtype=np.uint32)
+        assert len(mq) == n and len(cr) == n and len(ln) == n
+        return ReadScalars(mq.ctypes.data, cr.ctypes.data, ln.ctypes.data), (mq, cr, ln)
+
+    def count_batch(self, bases, seg_off, read_seg=None):
+        b, keep, n = self._batch(bases, seg_off, read_seg)
+        res, co, _ = self._outs(n, False)
+        self._check(self._L.cg_count_batch(self._h, C.byref(b), C.byref(co)), "cg_count_batch")
+        return res
+
+    def classify_batch(self, bases, seg_off, mean_q, compression, length, read_seg=None):
+        b, keep, n = self._batch(bases, seg_off, read_seg)
+        sc, keep2 = self._scalars(n, mean_q, compression, length)
+        res, co, ca = self._outs(n, True)
+        self._check(self._L.cg_classify_batch(self._h, C.byref(b), C.byref(sc), C.byref(co), C.byref(ca)), "cg_classify_batch")
+        return res
+
+    def eval_batch(self, num_hashes, counts, unique_counts, mean_q, compression, length):
+        n = len(num_hashes)
+        nh = np.ascontiguousarray(num_hashes, np.uint32); ct = np.ascontiguousarray(counts, np.uint32); uq = np.ascontiguousarray(unique_counts, np.uint32)
+        sc, keep2 = self._scalars(n, mean_q, compression, length)
+        res = dict(prob=np.zeros((n, self.ncat), np.float64), call=np.zeros(n, np.uint8), confidence=np.zeros(n, np.uint8))
+        ca = CallsOut(res["prob"].ctypes.data, res["call"].ctypes.data, res["confidence"].ctypes.data)
+        self._check(self._L.cg_eval_batch(self._h, n, nh.ctypes.data, ct.ctypes.data, uq.ctypes.data, C.byref(sc), C.byref(ca)), "cg_eval_batch")
+        return res
+
+    # staged path (device-resident inputs) -----------------------------------------------------------------------
+    def stage(self, bases, seg_off, mean_q=None, compression=None, length=None, read_seg=None):
+        b, keep, n = self._batch(bases, seg_off, read_seg)
+        sc = None
+        if mean_q is not None:
+            sc, keep2 = self._scalars(n, mean_q, compression, length)
+        self._check(self._L.cg_stage_batch(self._h, C.byref(b), C.byref(sc) if sc is not None else None), "cg_stage_batch")
+        self.sync()
+        self._staged_n = n
+
+    def run_staged(self, with_eval=True):
+        self._check(self._L.cg_run_staged(self._h, 1 if with_eval else 0), "cg_run_staged")
+
+    def fetch_staged(self, with_calls=True):
+        res, co, ca = self._outs(self._staged_n, with_calls)
+        self._check(self._L.cg_fetch_staged(self._h, C.byref(co), C.byref(ca) if ca is not None else None), "cg_fetch_staged")
+        return res
+
+    # test hooks ---------------------------------------------------------------------------------------------------
+    def debug_minimisers(self, seq) -> np.ndarray:
+        a = np.frombuffer(seq.encode() if isinstance(seq, str) else bytes(seq), dtype=np.uint8) if not isinstance(seq, np.ndarray) else np.ascontiguousarray(seq, np.uint8)
+        cap = max(len(a), 1)
+        out = np.zeros(cap, np.uint64); n = u64(0)
+        self._check(self._L.cg_debug_minimisers(self._h, _ptr(a) if len(a) else None, len(a), out.ctypes.data, cap, C.byref(n)), "cg_debug_minimisers")
+        return out[:n.value].copy()
+
+    def debug_query(self, values) -> np.ndarray:
+        v = np.ascontiguousarray(values, np.uint64)
+        out = np.zeros((len(v), self.bin_words), np.uint64)
+        self._check(self._L.cg_debug_query(self._h, v.ctypes.data, len(v), out.ctypes.data), "cg_debug_query")
+        return out
+
+    def debug_dump_filter(self) -> np.ndarray:
+        out = np.zeros(self.bin_size * self.bin_words, np.uint64)
+        self._check(self._L.cg_debug_dump_filter(self._h, out.ctypes.data), "cg_debug_dump_filter")
+        return out

@@ -1,0 +1,260 @@
+// charon_b200/csrc/charon_gpu.cu — libcharon_gpu.so: the C-ABI of include/charon_gpu.h over hand-written
+// sm_100a kernels.  Host part: filter upload / re-layout, batch staging, launches, result copies.
+// There is deliberately no CPU path: without a Blackwell device cg_create fails (CG_ERR_NO_DEVICE).
+#include "../../include/charon_gpu.h"
+
+#include <cub/device/device_scan.cuh>
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "count_kernel.cuh"
+#include "eval_kernel.cuh"
+#include "filter_build.cuh"
+
+namespace {
+
+thread_local std::string g_err;   // for cg_create failures (no handle yet)
+
+struct DevBuf {
+    void *p = nullptr;
+    size_t cap = 0;
+    int reserve(size_t bytes) {
+        if (bytes <= cap) return 0;
+        if (p) cudaFree(p);
+        p = nullptr; cap = 0;
+        size_t want = bytes + bytes / 8 + 256;
+        cudaError_t e = cudaMalloc(&p, want);
+        if (e != cudaSuccess) { p = nullptr; return int(e); }
+        cap = want;
+        return 0;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+    template <class T> T *as() const { return reinterpret_cast<T *>(p); }
+};
+
+}  // namespace
+
+struct cg_handle {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    bool own_stream = true;
+    cudaEvent_t ev[8] = {};
+    std::string err;
+    int sm_count = 0;
+    // index
+    uint32_t K = 0, W = 0, bins = 0, ncat = 0, bin_words = 0, hash_funs = 0, row_shift = 0, hash_shift = 0;
+    uint64_t bin_size = 0, technical_bins = 0;
+    int mode = 0;   // kernel MODE (row width class)
+    bool single_pass = false;
+    void *d_filter = nullptr;
+    size_t filter_bytes = 0;
+    uint8_t *d_bin_to_cat = nullptr;
+    uint8_t h_bin_to_cat[256];
+    // model
+    bool model_set = false;
+    int call_mode = 0;
+    cgk::ModelDev *d_models = nullptr;
+    float *d_pool = nullptr;
+    cg_thresholds thr{};
+    // batch buffers
+    DevBuf bases, seg_off, read_seg, num_hashes, counts, unique, prob, call, conf, mq, cr, len, counter, dbg, dbgn;
+    uint32_t staged_reads = 0, staged_segs = 0;
+    uint64_t staged_bases = 0;
+    bool staged_has_read_seg = false, staged_has_scalars = false;
+    // launch config
+    int grid_per_sm = 1;
+    // stats
+    cg_info info{};
+};
+
+namespace {
+
+int fail(cg_handle *h, int code, const char *fmt, ...) {
+    char buf[512];
+    va_list ap; va_start(ap, fmt); vsnprintf(buf, sizeof buf, fmt, ap); va_end(ap);
+    if (h) h->err = buf; else g_err = buf;
+    return code;
+}
+#define CU(h, call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) return fail(h, CG_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); } while (0)
+#define RSV(h, buf, bytes) do { int e_ = (buf).reserve(bytes); if (e_) return fail(h, CG_ERR_CUDA, "cudaMalloc(%zu) failed: %s", size_t(bytes), cudaGetErrorString(cudaError_t(e_))); } while (0)
+
+uint32_t ipow5(uint32_t e) { uint32_t r = 1; while (e--) r *= 5u; return r; }
+
+cgk::CountParams make_params(cg_handle *h) {
+    cgk::CountParams P{};
+    P.bases = h->bases.as<uint8_t>();
+    P.seg_off = h->seg_off.as<uint64_t>();
+    P.read_seg = h->staged_has_read_seg ? h->read_seg.as<uint32_t>() : nullptr;
+    P.n_reads = h->staged_reads;
+    P.K = h->K; P.Wv = h->W - h->K + 1;
+    P.kl = std::min<uint32_t>(h->K, 13); P.kh = h->K - P.kl;
+    P.p_lo_top = ipow5(P.kl - 1); P.p_hi_top = P.kh ? ipow5(P.kh - 1) : 0; P.p_kl = ipow5(P.kl);
+    P.seed = 0x8F3F73B5CF1C9ADEULL;   // seqan3::seed default
+    P.filter = h->d_filter; P.bin_size = h->bin_size; P.hash_shift = h->hash_shift; P.hash_funs = h->hash_funs;
+    P.row_shift = h->row_shift; P.bins = h->bins; P.ncat = h->ncat; P.single_pass = h->single_pass ? 1 : 0;
+    P.bin_to_cat = h->d_bin_to_cat;
+    P.num_hashes = h->num_hashes.as<uint32_t>(); P.counts = h->counts.as<uint32_t>(); P.unique_counts = h->unique.as<uint32_t>();
+    P.work_counter = h->counter.as<uint32_t>();
+    P.dbg_out = nullptr; P.dbg_cap = 0; P.dbg_n = nullptr;
+    return P;
+}
+
+template <int MODE> cudaError_t launch_count_mode(cg_handle *h, const cgk::CountParams &P, int grid) {
+    static bool attr_done[4] = {false, false, false, false};
+    if (!attr_done[MODE]) {
+        cudaError_t e = cudaFuncSetAttribute(cgk::count_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(cgk::SMEM_BYTES));
+        if (e != cudaSuccess) return e;
+        attr_done[MODE] = true;
+    }
+    cgk::count_kernel<MODE><<<grid, cgk::NT, cgk::SMEM_BYTES, h->stream>>>(P);
+    return cudaGetLastError();
+}
+template <int MODE> int occupancy_mode() {
+    int n = 0;
+    cudaFuncSetAttribute(cgk::count_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(cgk::SMEM_BYTES));
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, cgk::count_kernel<MODE>, cgk::NT, cgk::SMEM_BYTES);
+    return n;
+}
+
+int launch_count(cg_handle *h, const cgk::CountParams &P) {
+    if (P.n_reads == 0) return 0;
+    int grid = int(std::min<uint64_t>(uint64_t(h->sm_count) * h->grid_per_sm, P.n_reads));
+    CU(h, cudaMemsetAsync(h->counter.p, 0, 4, h->stream));
+    cudaError_t e;
+    switch (h->mode) {
+        case 0: e = launch_count_mode<0>(h, P, grid); break;
+        case 1: e = launch_count_mode<1>(h, P, grid); break;
+        case 2: e = launch_count_mode<2>(h, P, grid); break;
+        default: e = launch_count_mode<3>(h, P, grid); break;
+    }
+    if (e != cudaSuccess) return fail(h, CG_ERR_CUDA, "count kernel launch failed: %s", cudaGetErrorString(e));
+    h->info.count_grid = uint32_t(grid);
+    h->info.last_kernel_launches += 1;
+    return 0;
+}
+
+cgk::EvalParams make_eval(cg_handle *h, uint32_t n_reads) {
+    cgk::EvalParams E{};
+    E.n_reads = n_reads; E.ncat = h->ncat; E.mode = h->call_mode; E.models = h->d_models; E.pool = h->d_pool;
+    E.log_rate = std::log(300.0f);
+    const cg_thresholds &t = h->thr;
+    E.min_quality = t.min_quality; E.min_length = t.min_length; E.min_compression = t.min_compression;
+    E.confidence_threshold = t.confidence_threshold; E.confidence_probability_threshold = t.confidence_probability_threshold;
+    E.min_hits = t.min_hits; E.host_unique_prop_lo_threshold = t.host_unique_prop_lo_threshold;
+    E.min_proportion_difference = t.min_proportion_difference; E.min_prob_difference = t.min_prob_difference;
+    E.host_index = t.host_index;
+    E.num_hashes = h->num_hashes.as<uint32_t>(); E.counts = h->counts.as<uint32_t>(); E.unique_counts = h->unique.as<uint32_t>();
+    E.mean_quality = h->mq.as<float>(); E.compression = h->cr.as<float>(); E.length = h->len.as<uint32_t>();
+    E.prob = h->prob.as<double>(); E.call = h->call.as<uint8_t>(); E.confidence = h->conf.as<uint8_t>();
+    return E;
+}
+
+int launch_eval(cg_handle *h, uint32_t n_reads) {
+    if (!h->model_set) return fail(h, CG_ERR_STATE, "cg_set_model must be called before evaluation");
+    if (n_reads == 0) return 0;
+    cgk::EvalParams E = make_eval(h, n_reads);
+    const size_t pairs = size_t(n_reads) * h->ncat;
+    cgk::prob_kernel<<<unsigned((pairs + 127) / 128), 128, 0, h->stream>>>(E);
+    cgk::call_kernel<<<(n_reads + 127) / 128, 128, 0, h->stream>>>(E);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(h, CG_ERR_CUDA, "eval kernel launch failed: %s", cudaGetErrorString(e));
+    h->info.last_kernel_launches += 2;
+    return 0;
+}
+
+int reserve_outputs(cg_handle *h, uint32_t n_reads) {
+    const size_t n = std::max<uint32_t>(n_reads, 1);
+    RSV(h, h->num_hashes, n * 4); RSV(h, h->counts, n * h->ncat * 4); RSV(h, h->unique, n * h->ncat * 4);
+    RSV(h, h->prob, n * h->ncat * 8); RSV(h, h->call, n); RSV(h, h->conf, n);
+    RSV(h, h->mq, n * 4); RSV(h, h->cr, n * 4); RSV(h, h->len, n * 4);
+    RSV(h, h->counter, 16);
+    return 0;
+}
+
+int validate_batch(cg_handle *h, const cg_batch *b) {
+    if (!b || (!b->seg_off && b->n_segs) || (!b->bases && b->n_segs && b->seg_off[b->n_segs] > 0)) return fail(h, CG_ERR_ARG, "null batch pointers");
+    if (!b->read_seg && b->n_segs != b->n_reads) return fail(h, CG_ERR_ARG, "read_seg is NULL but n_segs != n_reads");
+    if (b->read_seg && (b->read_seg[0] != 0 || b->read_seg[b->n_reads] != b->n_segs)) return fail(h, CG_ERR_ARG, "read_seg must span [0, n_segs]");
+    return 0;
+}
+
+// H2D of one batch (src/dehost_main.cpp:335-339: the chunk of records handed to the loop)
+int stage(cg_handle *h, const cg_batch *b, const cg_read_scalars *sc) {
+    int rc = validate_batch(h, b);
+    if (rc) return rc;
+    const uint64_t nbases = b->n_segs ? b->seg_off[b->n_segs] : 0;
+    RSV(h, h->bases, nbases + 64);
+    RSV(h, h->seg_off, (size_t(b->n_segs) + 1) * 8);
+    if (b->read_seg) RSV(h, h->read_seg, (size_t(b->n_reads) + 1) * 4);
+    rc = reserve_outputs(h, b->n_reads);
+    if (rc) return rc;
+    CU(h, cudaEventRecord(h->ev[0], h->stream));
+    if (nbases) CU(h, cudaMemcpyAsync(h->bases.p, b->bases, nbases, cudaMemcpyHostToDevice, h->stream));
+    static const uint64_t zero_off[1] = {0};
+    CU(h, cudaMemcpyAsync(h->seg_off.p, b->n_segs ? b->seg_off : zero_off, (size_t(b->n_segs) + 1) * 8, cudaMemcpyHostToDevice, h->stream));
+    if (b->read_seg) CU(h, cudaMemcpyAsync(h->read_seg.p, b->read_seg, (size_t(b->n_reads) + 1) * 4, cudaMemcpyHostToDevice, h->stream));
+    h->staged_has_scalars = false;
+    if (sc && b->n_reads) {
+        if (!sc->mean_quality || !sc->compression || !sc->length) return fail(h, CG_ERR_ARG, "null read scalars");
+        CU(h, cudaMemcpyAsync(h->mq.p, sc->mean_quality, size_t(b->n_reads) * 4, cudaMemcpyHostToDevice, h->stream));
+        CU(h, cudaMemcpyAsync(h->cr.p, sc->compression, size_t(b->n_reads) * 4, cudaMemcpyHostToDevice, h->stream));
+        CU(h, cudaMemcpyAsync(h->len.p, sc->length, size_t(b->n_reads) * 4, cudaMemcpyHostToDevice, h->stream));
+        h->staged_has_scalars = true;
+    }
+    CU(h, cudaEventRecord(h->ev[1], h->stream));
+    h->staged_reads = b->n_reads; h->staged_segs = b->n_segs; h->staged_bases = nbases; h->staged_has_read_seg = b->read_seg != nullptr;
+    h->info.last_bases = nbases;
+    return 0;
+}
+
+int run(cg_handle *h, bool with_eval) {
+    h->info.last_kernel_launches = 0;
+    CU(h, cudaEventRecord(h->ev[2], h->stream));
+    int rc = launch_count(h, make_params(h));
+    if (rc) return rc;
+    CU(h, cudaEventRecord(h->ev[3], h->stream));
+    if (with_eval) {
+        if (!h->staged_has_scalars) return fail(h, CG_ERR_STATE, "evaluation needs the per-read scalars (mean_quality, compression, length)");
+        rc = launch_eval(h, h->staged_reads);
+        if (rc) return rc;
+    }
+    CU(h, cudaEventRecord(h->ev[4], h->stream));
+    return 0;
+}
+
+int fetch(cg_handle *h, const cg_counts_out *co, const cg_calls_out *ca) {
+    const size_t n = h->staged_reads, nc = h->ncat;
+    CU(h, cudaEventRecord(h->ev[5], h->stream));
+    if (n) {
+        if (co) {
+            if (co->num_hashes) CU(h, cudaMemcpyAsync(co->num_hashes, h->num_hashes.p, n * 4, cudaMemcpyDeviceToHost, h->stream));
+            if (co->counts) CU(h, cudaMemcpyAsync(co->counts, h->counts.p, n * nc * 4, cudaMemcpyDeviceToHost, h->stream));
+            if (co->unique_counts) CU(h, cudaMemcpyAsync(co->unique_counts, h->unique.p, n * nc * 4, cudaMemcpyDeviceToHost, h->stream));
+        }
+        if (ca) {
+            if (ca->probabilities) CU(h, cudaMemcpyAsync(ca->probabilities, h->prob.p, n * nc * 8, cudaMemcpyDeviceToHost, h->stream));
+            if (ca->call) CU(h, cudaMemcpyAsync(ca->call, h->call.p, n, cudaMemcpyDeviceToHost, h->stream));
+            if (ca->confidence) CU(h, cudaMemcpyAsync(ca->confidence, h->conf.p, n, cudaMemcpyDeviceToHost, h->stream));
+        }
+    }
+    CU(h, cudaEventRecord(h->ev[6], h->stream));
+    CU(h, cudaStreamSynchronize(h->stream));
+    float ms = 0;
+    if (cudaEventElapsedTime(&ms, h->ev[0], h->ev[1]) == cudaSuccess) h->info.last_h2d_ms = ms;
+    if (cudaEventElapsedTime(&ms, h->ev[2], h->ev[3]) == cudaSuccess) h->info.last_count_kernel_ms = ms;
+    if (cudaEventElapsedTime(&ms, h->ev[3], h->ev[4]) == cudaSuccess) h->info.last_eval_kernel_ms = ms;
+    if (cudaEventElapsedTime(&ms, h->ev[5], h->ev[6]) == cudaSuccess) h->info.last_d2h_ms = ms;
+    cudaGetLastError();
+    return 0;
+}
+
+}  // namespace
+
+#include "charon_gpu_api.inc"

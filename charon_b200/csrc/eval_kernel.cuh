@@ -1,0 +1,156 @@
+// charon_b200/csrc/eval_kernel.cuh — model evaluation + call logic (sm_100a).
+// Replaces ReadEntry::get_proportions / apply_model / call_host / call_category
+// (reference include/read_entry.hpp:140-150,157-291) and Model::prob / KDEParams::prob
+// (include/classify_stats.hpp:242-252,370-389).
+//
+// Arithmetic contract: proportions are float divisions of the integer counts; the KDE is a
+// *sequential float* sum in dataset order of float(exp(-z^2/2 in double)/sqrt(2 pi)); terms with |z| > 15 are
+// exactly +0.0f after the float rounding and are skipped (adding +0.0f never changes the running sum).
+// No fused multiply-add may be formed across the reference's separate float operations: explicit _rn intrinsics.
+#pragma once
+#include <cuda_runtime.h>
+#include <math_constants.h>
+#include <stdint.h>
+
+namespace cgk {
+
+struct ModelDev {            // one per category, device-resident
+    int32_t dist;            // 0 kde, 1 beta, 2 gamma
+    uint32_t pos_off, npos;  // offsets into the shared float pool
+    uint32_t neg_off, nneg;
+    float h_pos, h_neg;
+    float beta_pos[2], beta_neg[2];
+    float gamma_pos[3], gamma_neg[3];
+};
+
+struct EvalParams {
+    uint32_t n_reads, ncat;
+    int32_t mode;            // 0 dehost (call_host), 1 classify (call_category)
+    const ModelDev *models;
+    const float *pool;
+    float log_rate;          // logf(300.f) computed on the host exactly as the reference's float log
+    // thresholds
+    float min_quality; uint32_t min_length; float min_compression; int32_t confidence_threshold;
+    float confidence_probability_threshold; uint32_t min_hits; float host_unique_prop_lo_threshold;
+    float min_proportion_difference, min_prob_difference; uint32_t host_index;
+    // inputs
+    const uint32_t *num_hashes, *counts, *unique_counts;
+    const float *mean_quality, *compression; const uint32_t *length;
+    // outputs
+    double *prob; uint8_t *call; uint8_t *confidence;
+};
+
+__device__ __forceinline__ float kde_prob(const float *__restrict__ ds, uint32_t n, float h, float x) {
+    float total = 0.0f;
+    const double inv_sqrt = 2.5066282746310002;  // sqrt(2 * 3.141592653589793238463) in double
+    for (uint32_t i = 0; i < n; ++i) {
+        const float z = __fdiv_rn(__fsub_rn(x, ds[i]), h);
+        if (fabsf(z) > 15.0f) continue;                                 // term rounds to exactly +0.0f
+        const double zz = double(z) * double(z);                         // std::pow(float,2) -> exact in double
+        const float kf = float(exp(-zz / 2.0) / inv_sqrt);
+        total = __fadd_rn(total, kf);
+    }
+    return __fdiv_rn(total, __fmul_rn(h, float(n)));                    // NaN z falls through: exp(NaN) = NaN
+}
+
+__device__ __forceinline__ float dexp300(float x, float log_rate) {     // stats::dexp(float, 300)
+    if (isnan(x)) return CUDART_NAN_F;
+    if (x < 0.0f) return 0.0f;
+    const float a = __fsub_rn(log_rate, __fmul_rn(300.0f, x));
+    return float(exp(double(a)));                                        // correctly rounded float exp
+}
+__device__ __forceinline__ float dbeta_dev(float x, float a, float b) {
+    if (isnan(x)) return CUDART_NAN_F;
+    if (x < 0.0f || x > 1.0f) return 0.0f;
+    const float lbeta = __fsub_rn(__fadd_rn(lgammaf(a), lgammaf(b)), lgammaf(__fadd_rn(a, b)));
+    const float t = __fadd_rn(__fadd_rn(-lbeta, __fmul_rn(__fsub_rn(a, 1.0f), logf(x))), __fmul_rn(__fsub_rn(b, 1.0f), logf(__fsub_rn(1.0f, x))));
+    return expf(t);
+}
+__device__ __forceinline__ float dgamma_dev(float x, float shape, float scale) {
+    if (isnan(x)) return CUDART_NAN_F;
+    if (x < 0.0f) return 0.0f;
+    float t = __fsub_rn(-lgammaf(shape), __fmul_rn(shape, logf(scale)));
+    t = __fadd_rn(t, __fmul_rn(__fsub_rn(shape, 1.0f), logf(x)));
+    t = __fsub_rn(t, __fdiv_rn(x, scale));
+    return expf(t);
+}
+
+// one thread per (read, category): probabilities_[i] = 1.0 * Model::prob(unique_proportions_[i]).pos
+__global__ void prob_kernel(const EvalParams P) {
+    const size_t idx = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (idx >= size_t(P.n_reads) * P.ncat) return;
+    const uint32_t r = uint32_t(idx / P.ncat), c = uint32_t(idx % P.ncat);
+    const float x = __fdiv_rn(float(P.unique_counts[idx]), float(P.num_hashes[r]));   // read_entry.hpp:145
+    const ModelDev m = P.models[c];
+    const float p_err = dexp300(x, P.log_rate);
+    float p_pos, p_neg;
+    if (m.dist == 0) {
+        p_pos = kde_prob(P.pool + m.pos_off, m.npos, m.h_pos, x);
+        p_neg = kde_prob(P.pool + m.neg_off, m.nneg, m.h_neg, x);
+    } else if (m.dist == 2) {
+        p_pos = dgamma_dev(__fsub_rn(x, m.gamma_pos[1]), m.gamma_pos[0], m.gamma_pos[2]);
+        p_neg = dgamma_dev(__fsub_rn(x, m.gamma_neg[1]), m.gamma_neg[0], m.gamma_neg[2]);
+    } else {
+        p_pos = dbeta_dev(x, m.beta_pos[0], m.beta_pos[1]);
+        p_neg = dbeta_dev(x, m.beta_neg[0], m.beta_neg[1]);
+    }
+    if (x == 1.0f) p_pos = 1.0f;
+    const float total = __fadd_rn(__fadd_rn(p_err, p_pos), p_neg);
+    P.prob[idx] = double(__fdiv_rn(p_pos, total));
+}
+
+// one thread per read: call_host (mode 0) / call_category (mode 1)
+__global__ void call_kernel(const EvalParams P) {
+    const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= P.n_reads) return;
+    const uint32_t nc = P.ncat;
+    const uint32_t *uc = P.unique_counts + size_t(r) * nc;
+    const uint32_t *ct = P.counts + size_t(r) * nc;
+    const double *pr = P.prob + size_t(r) * nc;
+    const float nh = float(P.num_hashes[r]);
+    const float mq = P.mean_quality[r], cr = P.compression[r];
+    const uint32_t len = P.length[r];
+    uint8_t call = 255, conf = 0;
+    const int thr = int(int8_t(P.confidence_threshold));
+    if (P.mode == 0) {   // read_entry.hpp:218-269
+        const uint32_t host = P.host_index, other = 1u - host;
+        const double hu = double(__fdiv_rn(float(uc[host]), nh)), ou = double(__fdiv_rn(float(uc[other]), nh));
+        const double hp = pr[host], op = pr[other];
+        uint32_t first = host, second = other;
+        if (hu < ou) { first = other; second = host; }
+        const uint32_t raw = uc[first] - uc[second];   // unsigned wrap like the reference when NaN ordering misleads
+        conf = raw > 255u ? 255 : uint8_t(raw);
+        bool gate = !(int(conf) < thr) && !(mq < P.min_quality) && !(len < P.min_length) && !(cr < P.min_compression);
+        if (gate) {
+            const double dc = double(conf);
+            if (hu > ou && hu - ou > double(P.min_proportion_difference) && hp > op && hp - op > double(P.min_prob_difference) &&
+                fmax(hp * dc, dc) >= double(P.confidence_probability_threshold))
+                call = uint8_t(host);
+            else if (hu < double(P.host_unique_prop_lo_threshold) && hu < ou && ou - hu > double(P.min_proportion_difference) && hp < op &&
+                     op - hp > double(P.min_prob_difference) && fmax(op * dc, dc) >= double(P.confidence_probability_threshold))
+                call = uint8_t(other);
+        }
+    } else {             // read_entry.hpp:157-216
+        uint32_t first = 0, second = 1;
+        if (uc[second] > uc[first]) { first = 1; second = 0; }
+        for (uint32_t i = 2; i < nc; ++i)
+            if (uc[i] > uc[second]) {
+                second = i;
+                if (uc[second] > uc[first]) { const uint32_t t = first; first = second; second = t; }
+            }
+        const uint32_t raw = uc[first] - uc[second];
+        conf = raw > 255u ? 255 : uint8_t(raw);
+        if (!(mq < P.min_quality) && !(len < P.min_length) && !(cr < P.min_compression)) {
+            if (pr[second] == 0.0 && pr[first] > 0.0) call = uint8_t(first);
+            else if (int(conf) > thr && pr[first] > pr[second]) call = uint8_t(first);
+            const uint32_t fc = ct[first], sc = ct[second];
+            if (sc > fc || fc - sc < P.min_hits) call = 255;
+            const float fp = __fdiv_rn(float(fc), nh), sp = __fdiv_rn(float(sc), nh);
+            if (sp > fp || __fsub_rn(fp, sp) < P.min_proportion_difference) call = 255;
+        }
+    }
+    P.call[r] = call;
+    P.confidence[r] = conf;
+}
+
+}  // namespace cgk

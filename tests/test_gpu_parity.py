@@ -1,0 +1,186 @@
+"""GPU parity tests proper: the CUDA path, called through the C-ABI (ctypes), against the CPU oracle on the same
+seeded inputs.  Bit-exact for num_hashes / counts / unique counts / confidence / call; probabilities <= 1e-6 relative
+(north_star).  Run on the B200 box: pytest -m gpu."""
+import random
+import numpy as np
+import pytest
+import oracle
+from tests import common
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def small():
+    idx, refs = common.build_oracle_index([300_000, 300_000], [0, 1], ["host", "microbial"], seed=11)
+    gpu = common.gpu_from_oracle(idx)
+    import charon_b200
+    gpu.set_model(charon_b200.DehostOptions(), host_index=idx.host_index)
+    yield idx, refs, gpu
+    gpu.close()
+
+
+def test_filter_layout_roundtrip(small):
+    idx, refs, gpu = small
+    assert gpu.info().row_bits == 2 and gpu.info().single_pass == 1
+    assert np.array_equal(gpu.debug_dump_filter(), idx.rows())
+
+
+def test_membership_query_matches_oracle(small):
+    idx, refs, gpu = small
+    rng = np.random.default_rng(3)
+    vals = np.concatenate([oracle.minimisers(refs[0][:50_000]), oracle.minimisers(refs[1][:50_000]),
+                           rng.integers(0, 2**63, 5000, dtype=np.uint64)])
+    assert np.array_equal(gpu.debug_query(vals), idx.query(vals))
+
+
+def _tie_heavy_cases():
+    rng = random.Random(77)
+    rs = lambda n, a="ACGT": "".join(rng.choice(a) for _ in range(n))
+    cases = ["", "A", "ACGT" * 4 + "AC", "ACGT" * 4 + "ACG", rs(19), rs(20), rs(40), rs(41), rs(42), rs(64), rs(1000), rs(2984), rs(2985),
+             rs(2986), rs(3100), rs(9000), "A" * 5000, "AC" * 3000, "ACG" * 1500, "N" * 4000, rs(3000) + "N" * 3000 + rs(3000),
+             rs(3000, "AC"), rs(7000, "ACGTN"), ("ACGTTGCA" * 900)[:6111], rs(2940) + "A" * 200 + rs(3000), "acgtn" * 700 + "RYKMSWBDHVU" * 30]
+    for _ in range(12):
+        unit = rs(rng.randint(1, 12))
+        s = list((unit * 4000)[:rng.randint(2500, 9500)])
+        for i in range(len(s)):
+            if rng.random() < 0.02:
+                s[i] = rng.choice("ACGTN")
+        cases.append("".join(s))
+    return cases
+
+
+def test_minimiser_stream_matches_oracle_including_ties(small):
+    idx, refs, gpu = small
+    for s in _tie_heavy_cases():
+        want = np.sort(oracle.minimisers(s))
+        got = gpu.debug_minimisers(s)
+        assert np.array_equal(got, want), (len(s), s[:40], len(got), len(want))
+
+
+def test_long_read_tiling(small):
+    idx, refs, gpu = small
+    s = refs[0][1000:151_000]
+    assert np.array_equal(gpu.debug_minimisers(s), np.sort(oracle.minimisers(s)))
+
+
+def test_counts_and_calls_dehost_config1_like(small):
+    idx, refs, gpu = small
+    n, L = 2000, 5000
+    bases, seg_off, src = common.fixed_length_batch(5, refs, [0.45, 0.45], n, L)
+    rng = np.random.default_rng(1)
+    mq, cr = common.scalars(n, rng)
+    length = np.full(n, L, np.uint32)
+    want = idx.classify_batch(bases, seg_off, mean_q=mq, compression=cr)
+    got = gpu.classify_batch(bases, seg_off, mq, cr, length)
+    common.assert_parity(got, want)
+    assert (want["call"] != 255).sum() > n // 2            # the workload really classifies
+    only_counts = gpu.count_batch(bases, seg_off)
+    common.assert_parity(only_counts, want)
+    ev = gpu.eval_batch(want["num_hashes"], want["counts"], want["unique_counts"], mq, cr, length)
+    assert np.array_equal(ev["call"], want["call"]) and np.array_equal(ev["confidence"], want["confidence"])
+
+
+def test_ragged_empty_short_and_paired(small):
+    idx, refs, gpu = small
+    rng = np.random.default_rng(9)
+    pieces = []
+    for ln in [0, 1, 18, 19, 20, 41, 42, 139, 140, 141, 500, 2985, 2986, 6000, 12_345, 0, 33]:
+        st = int(rng.integers(0, 200_000))
+        pieces.append(refs[int(rng.integers(0, 2))][st:st + ln].copy())
+    bases, seg_off = common.ragged_batch(rng, pieces)
+    n = len(pieces)
+    mq, cr = common.scalars(n)
+    length = np.diff(seg_off).astype(np.uint32)
+    want = idx.classify_batch(bases, seg_off, mean_q=mq, compression=cr)
+    got = gpu.classify_batch(bases, seg_off, mq, cr, length)
+    common.assert_parity(got, want)
+    assert want["num_hashes"][0] == 0 and np.isnan(got["prob"][0]).all()
+    # paired: two segments per read, minimisers of mate 1 then mate 2 into one entry (src/dehost_main.cpp:458-465)
+    pieces2 = pieces[:16]
+    bases2, seg_off2 = common.ragged_batch(rng, pieces2)
+    read_seg = np.arange(0, 17, 2, dtype=np.uint32)
+    mq2, cr2 = common.scalars(8)
+    len2 = np.add.reduceat(np.diff(seg_off2), read_seg[:-1]).astype(np.uint32)
+    want2 = idx.classify_batch(bases2, seg_off2, read_seg=read_seg, mean_q=mq2, compression=cr2)
+    got2 = gpu.classify_batch(bases2, seg_off2, mq2, cr2, len2, read_seg=read_seg)
+    common.assert_parity(got2, want2)
+
+
+def test_empty_batch(small):
+    idx, refs, gpu = small
+    res = gpu.count_batch(np.zeros(0, np.uint8), np.zeros(1, np.uint64))
+    assert res["num_hashes"].shape == (0,)
+
+
+@pytest.mark.parametrize("nbins,bin_cat,cats", [
+    (3, [0, 1, 1], ["host", "microbial"]),                       # multi-bin category -> two-pass best-bin path, 4-bit rows
+    (7, [0, 1, 2, 0, 1, 2, 2], ["a", "host", "c"]),              # 8-bit rows
+    (20, [i % 5 for i in range(20)], [f"c{i}" for i in range(5)]),  # 32-bit rows
+    (40, [i % 40 for i in range(40)], [f"c{i}" for i in range(40)]),  # 64-bit rows, one bin per category
+    (70, [i % 9 for i in range(70)], [f"c{i}" for i in range(9)]),   # 128-bit rows, two mask words
+    (255, list(range(255)), [f"c{i}" for i in range(255)]),          # 256-bit rows (config 4 shape)
+    (200, [i % 100 for i in range(200)], [f"c{i}" for i in range(100)]),
+])
+def test_many_bins_classify(nbins, bin_cat, cats):
+    import charon_b200
+    idx, refs = common.build_oracle_index([20_000] * nbins, bin_cat, cats, seed=100 + nbins)
+    gpu = common.gpu_from_oracle(idx)
+    try:
+        assert np.array_equal(gpu.debug_dump_filter(), idx.rows())
+        gpu.set_model(charon_b200.ClassifyOptions(), host_index=0)
+        n, L = 300, 3000
+        fr = [0.9 / nbins] * nbins
+        bases, seg_off, src = common.fixed_length_batch(6, refs, fr, n, L)
+        mq, cr = common.scalars(n)
+        opts = oracle.default_options(dehost=False)
+        want = idx.classify_batch(bases, seg_off, mean_q=mq, compression=cr, opts=opts)
+        got = gpu.classify_batch(bases, seg_off, mq, cr, np.full(n, L, np.uint32))
+        # classify uses beta densities through lgamma/log/exp in float: best-effort 1e-4; integers exact
+        common.assert_parity(got, want, prob_rtol=2e-4)
+    finally:
+        gpu.close()
+
+
+@pytest.mark.parametrize("k,w", [(19, 19), (5, 12), (13, 40), (14, 14), (26, 60), (11, 255)])
+def test_other_k_w(k, w):
+    idx, refs = common.build_oracle_index([50_000, 50_000], [0, 1], ["human", "other"], seed=55, k=k, w=w)
+    gpu = common.gpu_from_oracle(idx)
+    try:
+        for s in [refs[0][:7000], refs[1][100:400], np.frombuffer(b"A" * 3000, np.uint8), np.frombuffer(b"ACGTN" * 900, np.uint8)]:
+            assert np.array_equal(gpu.debug_minimisers(s), np.sort(oracle.minimisers(s, k, w))), (k, w, len(s))
+        bases, seg_off, _ = common.fixed_length_batch(2, refs, [0.5, 0.4], 200, 1500)
+        common.assert_parity(gpu.count_batch(bases, seg_off), idx.classify_batch(bases, seg_off))
+    finally:
+        gpu.close()
+
+
+def test_sd_vector_payload_decoded_on_device(tmp_path, small):
+    """The .idx payload (sdsl sd_vector low/high words) is decoded on the GPU to the same filter bits."""
+    idx, refs, gpu = small
+    rows = idx.rows()
+    pos = np.flatnonzero(np.unpackbits(rows.view(np.uint8), bitorder="little")).astype(np.uint64)
+    n, m = idx.technical_bins * idx.bin_size, len(pos)
+    logm, logn = int(m).bit_length(), int(n).bit_length()
+    if logm == logn:
+        logm -= 1
+    wl = logn - logm
+    lowvals = pos & np.uint64((1 << wl) - 1)
+    low_bits = m * wl
+    lowbits = ((lowvals[:, None] >> np.arange(wl, dtype=np.uint64)) & np.uint64(1)).astype(np.uint8).reshape(-1)
+    low = np.packbits(np.pad(lowbits, (0, (-len(lowbits)) % 64)), bitorder="little").view(np.uint64)
+    high_bits = m + (1 << logm)
+    hb = np.zeros(high_bits + (-high_bits) % 64, np.uint8)
+    hb[(pos >> np.uint64(wl)) + np.arange(m, dtype=np.uint64)] = 1
+    high = np.packbits(hb, bitorder="little").view(np.uint64)
+    import charon_b200
+    g2 = charon_b200.GpuClassifier(k=idx.k, w=idx.w, bins=idx.bins, bin_size=idx.bin_size, hash_funs=3, bin_to_cat=idx.bin_to_cat,
+                                   ncat=idx.ncat, sd=(low, low_bits, high, high_bits, wl))
+    try:
+        assert np.array_equal(g2.debug_dump_filter(), rows)
+    finally:
+        g2.close()
+    bad = high.copy(); bad[0] |= np.uint64(1) << np.uint64(63)     # an extra set bit must be rejected, not ignored
+    with pytest.raises(charon_b200.CharonGpuError):
+        charon_b200.GpuClassifier(k=idx.k, w=idx.w, bins=idx.bins, bin_size=idx.bin_size, hash_funs=3, bin_to_cat=idx.bin_to_cat,
+                                  ncat=idx.ncat, sd=(low, low_bits, bad, high_bits, wl))
