@@ -14,6 +14,11 @@ LIB_PATH = os.path.join(_HERE, "libcharon_gpu.so")
 u8, u16, u32, u64, i32, f32, f64, vp = C.c_uint8, C.c_uint16, C.c_uint32, C.c_uint64, C.c_int32, C.c_float, C.c_double, C.c_void_p
 
 
+class BuildDesc(C.Structure):
+    _fields_ = [("kmer_size", u8), ("window_size", u8), ("hash_funs", u32), ("max_fpr", f64), ("max_bits", u64), ("bases", vp),
+                ("rec_off", vp), ("rec_bin", vp), ("n_records", u32), ("bins", u32), ("ncat", u16), ("bin_to_cat", vp)]
+
+
 class IndexDesc(C.Structure):
     _fields_ = [("kmer_size", u8), ("window_size", u8), ("bins", u64), ("technical_bins", u64), ("bin_size", u64), ("hash_shift", u64),
                 ("bin_words", u64), ("hash_funs", u64), ("filter_format", i32), ("rows", vp), ("sd_low", vp), ("sd_low_bits", u64),
@@ -48,14 +53,14 @@ class CallsOut(C.Structure):
 
 
 class Info(C.Structure):
-    _fields_ = [("filter_bytes", u64), ("row_bits", u32), ("single_pass", u32), ("sm_count", u32), ("count_grid", u32),
+    _fields_ = [("bin_size", u64), ("filter_bytes", u64), ("row_bits", u32), ("single_pass", u32), ("sm_count", u32), ("count_grid", u32),
                 ("count_block", u32), ("count_smem_bytes", u32), ("last_minimisers", u64), ("last_bases", u64),
                 ("last_kernel_launches", u32), ("last_count_kernel_ms", f32), ("last_eval_kernel_ms", f32), ("last_h2d_ms", f32),
                 ("last_d2h_ms", f32)]
 
 
-EXPORTS = ["cg_create", "cg_destroy", "cg_last_error", "cg_set_stream", "cg_sync", "cg_set_model", "cg_count_batch", "cg_eval_batch",
-           "cg_classify_batch", "cg_stage_batch", "cg_run_staged", "cg_fetch_staged", "cg_get_info", "cg_debug_minimisers",
+EXPORTS = ["cg_create", "cg_build_index", "cg_destroy", "cg_last_error", "cg_set_stream", "cg_sync", "cg_set_model", "cg_count_batch", "cg_eval_batch",
+           "cg_classify_batch", "cg_stage_batch", "cg_run_staged", "cg_fetch_staged", "cg_get_info", "cg_host_alloc", "cg_host_free", "cg_timer_start", "cg_timer_stop", "cg_debug_minimisers",
            "cg_debug_query", "cg_debug_dump_filter"]
 
 _lib = None
@@ -72,6 +77,7 @@ def load_library():
     L = C.CDLL(LIB_PATH)
     P = C.POINTER
     L.cg_create.argtypes = [i32, P(IndexDesc), C.c_size_t, P(vp)]
+    L.cg_build_index.argtypes = [i32, P(BuildDesc), C.c_size_t, vp, P(vp)]
     L.cg_destroy.argtypes = [vp]; L.cg_destroy.restype = None
     L.cg_last_error.argtypes = [vp]; L.cg_last_error.restype = C.c_char_p
     L.cg_set_stream.argtypes = [vp, vp]
@@ -84,6 +90,10 @@ def load_library():
     L.cg_run_staged.argtypes = [vp, i32]
     L.cg_fetch_staged.argtypes = [vp, P(CountsOut), P(CallsOut)]
     L.cg_get_info.argtypes = [vp, P(Info)]
+    L.cg_host_alloc.argtypes = [C.c_size_t, P(vp)]
+    L.cg_host_free.argtypes = [vp]; L.cg_host_free.restype = None
+    L.cg_timer_start.argtypes = [vp]
+    L.cg_timer_stop.argtypes = [vp, P(f32), P(f32), P(f32), P(u32)]
     L.cg_debug_minimisers.argtypes = [vp, vp, u64, vp, u64, P(u64)]
     L.cg_debug_query.argtypes = [vp, vp, u64, vp]
     L.cg_debug_dump_filter.argtypes = [vp, vp]
@@ -93,6 +103,34 @@ def load_library():
 
 class CharonGpuError(RuntimeError):
     pass
+
+
+def pinned_array(shape, dtype):
+    """numpy array backed by cudaHostAlloc'd (pinned) memory; freed when the array is garbage collected."""
+    L = load_library()
+    dt = np.dtype(dtype)
+    n = int(np.prod(shape)) * dt.itemsize
+    p = vp()
+    rc = L.cg_host_alloc(n, C.byref(p))
+    if rc != 0:
+        raise CharonGpuError(f"cg_host_alloc failed ({rc}): {L.cg_last_error(None).decode()}")
+    buf = (C.c_char * max(n, 1)).from_address(p.value)
+    arr = np.frombuffer(buf, dtype=dt, count=int(np.prod(shape))).reshape(shape)
+
+    class _Owner:
+        def __init__(self, ptr):
+            self.ptr = ptr
+
+        def __del__(self):
+            try:
+                L.cg_host_free(self.ptr)
+            except Exception:
+                pass
+    _PINNED[id(buf)] = _Owner(p)          # keep the owner alive as long as the process (bench buffers)
+    return arr
+
+
+_PINNED = {}
 
 
 def _ptr(a):
@@ -124,6 +162,29 @@ class ClassifyOptions(DehostOptions):
 class GpuClassifier:
     """One handle = one GPU holding the compacted filter.  Mirrors what Index::agent() + Result give the
     reference's loop (src/dehost_main.cpp:321,331): `count_batch`, `classify_batch`."""
+
+    @classmethod
+    def from_references(cls, records, rec_bin, bin_to_cat, ncat, k=19, w=41, hash_funs=3, max_fpr=0.01, device=0, mem_budget=0):
+        """`charon index` data path on the GPU (cg_build_index): records = list of uint8 arrays, rec_bin[i] = bin."""
+        L = load_library()
+        self = cls.__new__(cls)
+        self._L = L
+        cat = np.ascontiguousarray(np.concatenate(records)) if len(records) > 1 else np.ascontiguousarray(records[0], dtype=np.uint8)
+        off = np.zeros(len(records) + 1, dtype=np.uint64); off[1:] = np.cumsum([len(r) for r in records])
+        rb = np.ascontiguousarray(rec_bin, dtype=np.uint32); b2c = np.ascontiguousarray(bin_to_cat, dtype=np.uint8)
+        d = BuildDesc(k, w, hash_funs, max_fpr, 0, cat.ctypes.data, off.ctypes.data, rb.ctypes.data, len(records), len(b2c), ncat, b2c.ctypes.data)
+        hpb = np.zeros(len(b2c), np.uint64)
+        h = vp()
+        rc = L.cg_build_index(device, C.byref(d), mem_budget, hpb.ctypes.data, C.byref(h))
+        if rc != 0:
+            raise CharonGpuError(f"cg_build_index failed ({rc}): {L.cg_last_error(None).decode()}")
+        self._h = h
+        self._keep = []; self._model_keep = None
+        self.hashes_per_bin = hpb
+        self.k, self.w, self.bins, self.ncat = k, w, len(b2c), ncat
+        self.bin_words = (self.bins + 63) // 64
+        self.bin_size = int(self.info().bin_size)
+        return self
 
     def __init__(self, *, k, w, bins, bin_size, hash_funs, bin_to_cat, ncat, rows=None, sd=None, device=0, mem_budget=0):
         L = load_library()
@@ -268,6 +329,15 @@ class GpuClassifier:
         res, co, ca = self._outs(self._staged_n, with_calls)
         self._check(self._L.cg_fetch_staged(self._h, C.byref(co), C.byref(ca) if ca is not None else None), "cg_fetch_staged")
         return res
+
+    def timer_start(self):
+        self._check(self._L.cg_timer_start(self._h), "cg_timer_start")
+
+    def timer_stop(self):
+        """-> (total_ms, count_kernel_ms_sum, eval_kernel_ms_sum, n_runs) measured with CUDA events on the handle's stream"""
+        t, c, e, n = f32(0), f32(0), f32(0), u32(0)
+        self._check(self._L.cg_timer_stop(self._h, C.byref(t), C.byref(c), C.byref(e), C.byref(n)), "cg_timer_stop")
+        return t.value, c.value, e.value, n.value
 
     # test hooks ---------------------------------------------------------------------------------------------------
     def debug_minimisers(self, seq) -> np.ndarray:

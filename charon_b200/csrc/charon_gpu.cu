@@ -3,7 +3,9 @@
 // There is deliberately no CPU path: without a Blackwell device cg_create fails (CG_ERR_NO_DEVICE).
 #include "../../include/charon_gpu.h"
 
+#include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
+#include <cub/device/device_select.cuh>
 #include <cuda_runtime.h>
 
 #include <algorithm>
@@ -72,6 +74,15 @@ struct cg_handle {
     int grid_per_sm = 1;
     // stats
     cg_info info{};
+    // cg_timer_*: one outer event pair + three events per run recorded while timing
+    bool timing = false;
+    cudaEvent_t t0 = nullptr, t1 = nullptr;
+    std::vector<cudaEvent_t> tev;
+    size_t tev_used = 0;
+    cudaEvent_t next_tev() {
+        if (tev_used == tev.size()) { cudaEvent_t e = nullptr; cudaEventCreate(&e); tev.push_back(e); }
+        return tev[tev_used++];
+    }
 };
 
 namespace {
@@ -102,6 +113,7 @@ cgk::CountParams make_params(cg_handle *h) {
     P.bin_to_cat = h->d_bin_to_cat;
     P.num_hashes = h->num_hashes.as<uint32_t>(); P.counts = h->counts.as<uint32_t>(); P.unique_counts = h->unique.as<uint32_t>();
     P.work_counter = h->counter.as<uint32_t>();
+    P.seg_len = nullptr;
     P.dbg_out = nullptr; P.dbg_cap = 0; P.dbg_n = nullptr;
     return P;
 }
@@ -217,15 +229,18 @@ int stage(cg_handle *h, const cg_batch *b, const cg_read_scalars *sc) {
 int run(cg_handle *h, bool with_eval) {
     h->info.last_kernel_launches = 0;
     CU(h, cudaEventRecord(h->ev[2], h->stream));
+    if (h->timing) CU(h, cudaEventRecord(h->next_tev(), h->stream));
     int rc = launch_count(h, make_params(h));
     if (rc) return rc;
     CU(h, cudaEventRecord(h->ev[3], h->stream));
+    if (h->timing) CU(h, cudaEventRecord(h->next_tev(), h->stream));
     if (with_eval) {
         if (!h->staged_has_scalars) return fail(h, CG_ERR_STATE, "evaluation needs the per-read scalars (mean_quality, compression, length)");
         rc = launch_eval(h, h->staged_reads);
         if (rc) return rc;
     }
     CU(h, cudaEventRecord(h->ev[4], h->stream));
+    if (h->timing) CU(h, cudaEventRecord(h->next_tev(), h->stream));
     return 0;
 }
 

@@ -23,6 +23,7 @@ struct CountParams {
     const uint8_t *bases;
     const uint64_t *seg_off;
     const uint32_t *read_seg;   // may be null: one segment per read
+    const uint64_t *seg_len;    // may be null: segment s = [seg_off[s], seg_off[s+1]); else [seg_off[s], seg_off[s]+seg_len[s])
     uint32_t n_reads;
     // minimiser parameters
     uint32_t K, Wv;             // k-mer size, window in k-mers (w - k + 1)
@@ -38,7 +39,8 @@ struct CountParams {
     // outputs
     uint32_t *num_hashes, *counts, *unique_counts;
     uint32_t *work_counter;
-    // debug (test hook): emitted minimiser values
+    // emission capture (index construction + test hook): emitted minimiser values appended to dbg_out;
+    // filter == nullptr skips the membership query entirely (capture-only launch)
     uint64_t *dbg_out;
     unsigned long long dbg_cap;
     unsigned long long *dbg_n;
@@ -164,6 +166,7 @@ __global__ void __launch_bounds__(NT) count_kernel(const CountParams P) {
     __shared__ uint32_t s_read, s_nlist, s_susp, s_nhash;
     __shared__ long long s_carry_pos;
     __shared__ uint64_t s_carry_val;
+    __shared__ unsigned long long s_dbg_base;
 
     const uint32_t tid = threadIdx.x;
     const uint32_t lane = tid & 31u;
@@ -196,7 +199,7 @@ __global__ void __launch_bounds__(NT) count_kernel(const CountParams P) {
 
             for (uint32_t seg = seg0; seg < seg1; ++seg) {
                 const uint64_t sbase = P.seg_off[seg];
-                const uint64_t slen = P.seg_off[seg + 1] - sbase;
+                const uint64_t slen = P.seg_len ? P.seg_len[seg] : P.seg_off[seg + 1] - sbase;
                 if (slen < K) continue;
                 const uint64_t nkm = slen - K + 1;
                 const uint32_t Wp = uint32_t(nkm < P.Wv ? nkm : P.Wv);
@@ -329,12 +332,17 @@ __global__ void __launch_bounds__(NT) count_kernel(const CountParams P) {
                     prev_val = s_carry_val;
                     // ---- phase 3: membership query + counting ------------------------------------
                     const uint32_t nl = s_nlist;
+                    if (P.dbg_out && do_tot) {   // capture: one global atomic per tile
+                        if (tid == 0) s_dbg_base = atomicAdd(P.dbg_n, (unsigned long long)nl);
+                        __syncthreads();
+                        for (uint32_t i = tid; i < nl; i += NT) {
+                            const unsigned long long slot = s_dbg_base + i;
+                            if (slot < P.dbg_cap) P.dbg_out[slot] = S.v[S.ppos[i]];
+                        }
+                    }
+                    if (P.filter)
                     for (uint32_t i = tid; i < nl; i += NT) {
                         const uint64_t hv = S.v[S.ppos[i]];
-                        if (P.dbg_out && do_tot) {
-                            unsigned long long slot = atomicAdd(P.dbg_n, 1ull);
-                            if (slot < P.dbg_cap) P.dbg_out[slot] = hv;
-                        }
                         const Mask<NW> m = bulk_contains<MODE>(P, hv);
                         if (small_bins) {
                             const uint32_t m0 = uint32_t(m.w[0]);

@@ -106,6 +106,24 @@ __global__ void sd_decode_kernel(const SdDecodeParams P) {
     }
 }
 
+// seqan3 interleaved_bloom_filter::emplace(value, bin) for an array of values (reference src/index_main.cpp:252-254)
+__global__ void ibf_insert_kernel(const uint64_t *__restrict__ values, uint64_t n, uint32_t bin, uint64_t bin_size, uint32_t hash_shift,
+                                  uint32_t hash_funs, uint32_t row_shift, void *filter) {
+    const uint32_t rb = 1u << row_shift;
+    for (uint64_t i = blockIdx.x * uint64_t(blockDim.x) + threadIdx.x; i < n; i += uint64_t(gridDim.x) * blockDim.x) {
+        const uint64_t v = values[i];
+        for (uint32_t f = 0; f < hash_funs; ++f) {
+            const uint64_t row = ibf_row(v, c_ibf_seeds[f], hash_shift, bin_size);
+            if (rb <= 32) {
+                const uint64_t bit = (row << row_shift) + bin;
+                atomicOr(reinterpret_cast<uint32_t *>(filter) + (bit >> 5), 1u << (uint32_t(bit) & 31u));
+            } else {
+                atomicOr(reinterpret_cast<unsigned long long *>(filter) + row * (rb / 64) + (bin >> 6), 1ull << (bin & 63u));
+            }
+        }
+    }
+}
+
 // membership masks for raw hash values (test hook cg_debug_query): expands to the seqan3 binning_bitvector layout
 template <int MODE>
 __global__ void query_kernel(const CountParams P, const uint64_t *__restrict__ values, uint64_t n, uint32_t bin_words,

@@ -123,10 +123,31 @@ typedef struct cg_calls_out {
     uint8_t *confidence;       /* [n_reads] */
 } cg_calls_out;
 
+/* Reference sequences for building an index on the device (the `charon index` data path:
+ * src/index_main.cpp:118-160 count_and_store_hashes, :238-263 build_index, src/utils.cpp:75-90 bin_size_in_bits). */
+typedef struct cg_build_desc {
+    uint8_t kmer_size, window_size;  /* include/index_arguments.hpp:16-17 (41 / 19) */
+    uint32_t hash_funs;              /* include/index_arguments.hpp:21 (3) */
+    double max_fpr;                  /* include/index_arguments.hpp:22 (0.01) */
+    uint64_t max_bits;               /* include/index_arguments.hpp:20 (2^32 - 3); 0 = that default */
+    const char *bases;               /* concatenated records (raw ASCII) */
+    const uint64_t *rec_off;         /* n_records + 1 */
+    const uint32_t *rec_bin;         /* bin of each record */
+    uint32_t n_records;
+    uint32_t bins;
+    uint16_t ncat;
+    const uint8_t *bin_to_cat;
+} cg_build_desc;
+
 /* ---- lifetime -------------------------------------------------------------------------- */
 /* Replaces load_index' in-memory IBF + Index::agent() (src/load_index.cpp:8-15, include/index.hpp:110-112):
  * uploads the filter, re-lays it out column-compacted in HBM.  mem_budget_bytes = 0: whole device. */
 int cg_create(int device, const cg_index_desc *desc, size_t mem_budget_bytes, cg_handle **out);
+/* Builds the filter ON the GPU from reference sequences: minimiser hashing with the classify kernels, distinct
+ * hashes per bin (sort + unique), bin_size from the largest bin, atomic-OR insertion.  hashes_per_bin[bins] receives
+ * InputStats::hashes_per_bin (include/input_stats.hpp:19).  The handle is then ready for classification; the filter
+ * can be exported with cg_debug_dump_filter to write an .idx file. */
+int cg_build_index(int device, const cg_build_desc *desc, size_t mem_budget_bytes, uint64_t *hashes_per_bin, cg_handle **out);
 void cg_destroy(cg_handle *h);
 const char *cg_last_error(const cg_handle *h);
 /* Use an externally created cudaStream_t (e.g. torch's current stream) for all work; NULL = own stream. */
@@ -152,8 +173,17 @@ int cg_stage_batch(cg_handle *h, const cg_batch *batch, const cg_read_scalars *s
 int cg_run_staged(cg_handle *h, int with_eval);                                            /* kernels only, async */
 int cg_fetch_staged(cg_handle *h, const cg_counts_out *counts_out, const cg_calls_out *calls_out); /* D2H + sync */
 
+/* ---- pinned host memory + device-side timing (CUDA events on the handle's stream) ---------- */
+int cg_host_alloc(size_t bytes, void **out);   /* cudaHostAlloc: pinned buffers for cg_batch / outputs */
+void cg_host_free(void *p);
+/* Everything enqueued on the handle between start and stop is timed with one event pair; additionally every
+ * cg_run_staged / cg_classify_batch in between records per-launch events so the count kernel's own duration is known. */
+int cg_timer_start(cg_handle *h);
+int cg_timer_stop(cg_handle *h, float *total_ms, float *count_kernel_ms_sum, float *eval_kernel_ms_sum, uint32_t *n_runs);
+
 /* ---- introspection ----------------------------------------------------------------------- */
 typedef struct cg_info {
+    uint64_t bin_size;            /* IBF rows (bits per bin) */
     uint64_t filter_bytes;        /* compacted filter size in HBM */
     uint32_t row_bits;            /* compacted row width (power of two >= bins) */
     uint32_t single_pass;         /* 1 when every category owns exactly one bin (best bin static) */

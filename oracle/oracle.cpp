@@ -222,16 +222,23 @@ Index build_index(const std::vector<std::pair<std::string, std::string>> &, cons
     idx.summary.categories = category_order;
     std::vector<std::vector<uint64_t>> hashes(nb);
     (void)threads;
+    // records are hashed independently (the reference parallelises over files, :129); per-bin distinct set afterwards
+    std::vector<std::pair<size_t, size_t>> flat;
+    for (size_t b = 0; b < nb; ++b) for (size_t r = 0; r < bin_sequences[b].size(); ++r) flat.emplace_back(b, r);
+    std::vector<std::vector<uint64_t>> per_rec(flat.size());
+#pragma omp parallel for schedule(dynamic) num_threads(threads)
+    for (size_t f = 0; f < flat.size(); ++f) {
+        const std::string &rec = bin_sequences[flat[f].first][flat[f].second];
+        std::vector<uint8_t> ranks(rec.size());
+        for (size_t i = 0; i < rec.size(); ++i) ranks[i] = dna5_rank((unsigned char)rec[i]);
+        minimiser_hash(ranks.data(), ranks.size(), k, w, per_rec[f]);
+        std::sort(per_rec[f].begin(), per_rec[f].end());
+        per_rec[f].erase(std::unique(per_rec[f].begin(), per_rec[f].end()), per_rec[f].end());
+    }
 #pragma omp parallel for schedule(dynamic) num_threads(threads)
     for (size_t b = 0; b < nb; ++b) {
         std::vector<uint64_t> &hs = hashes[b];
-        std::vector<uint8_t> ranks; std::vector<uint64_t> mins;
-        for (const std::string &rec : bin_sequences[b]) {
-            ranks.resize(rec.size());
-            for (size_t i = 0; i < rec.size(); ++i) ranks[i] = dna5_rank((unsigned char)rec[i]);
-            minimiser_hash(ranks.data(), ranks.size(), k, w, mins);
-            hs.insert(hs.end(), mins.begin(), mins.end());
-        }
+        for (size_t f = 0; f < flat.size(); ++f) if (flat[f].first == b) { hs.insert(hs.end(), per_rec[f].begin(), per_rec[f].end()); std::vector<uint64_t>().swap(per_rec[f]); }
         std::sort(hs.begin(), hs.end());
         hs.erase(std::unique(hs.begin(), hs.end()), hs.end());  // unordered_set<uint64_t> semantics (:141-149)
     }
@@ -245,9 +252,11 @@ Index build_index(const std::vector<std::pair<std::string, std::string>> &, cons
         max_hashes = std::max<uint64_t>(max_hashes, hashes[b].size());
     }
     idx.ibf.init(nb, bin_size_in_bits(max_hashes), 3);   // index_arguments.hpp:20-22, index_main.cpp:240-245
-#pragma omp parallel for schedule(dynamic) num_threads(threads)
-    for (size_t b = 0; b < nb; ++b)
-        for (uint64_t h : hashes[b]) idx.ibf.emplace(h, b);
+    for (size_t b = 0; b < nb; ++b) {
+        const std::vector<uint64_t> &hs = hashes[b];
+#pragma omp parallel for schedule(static) num_threads(threads)
+        for (size_t i = 0; i < hs.size(); ++i) idx.ibf.emplace(hs[i], b);   // atomic OR inside
+    }
     return idx;
 }
 

@@ -184,3 +184,21 @@ def test_sd_vector_payload_decoded_on_device(tmp_path, small):
     with pytest.raises(charon_b200.CharonGpuError):
         charon_b200.GpuClassifier(k=idx.k, w=idx.w, bins=idx.bins, bin_size=idx.bin_size, hash_funs=3, bin_to_cat=idx.bin_to_cat,
                                   ncat=idx.ncat, sd=(low, low_bits, bad, high_bits, wl))
+
+
+@pytest.mark.parametrize("nbins,lens", [(2, [400_000, 150_000]), (5, [30_000, 70_000, 10, 200_000, 18]), (70, [5_000] * 70)])
+def test_index_built_on_gpu_equals_oracle_index(nbins, lens):
+    """cg_build_index (device-side `charon index` data path) produces the same bin_size, distinct-hash counts and
+    filter bits as the oracle's restatement of src/index_main.cpp:118-263."""
+    import charon_b200
+    cats = [f"c{i}" for i in range(min(nbins, 3))]
+    bin_cat = [i % len(cats) for i in range(nbins)]
+    idx, refs = common.build_oracle_index(lens, bin_cat, cats, seed=900 + nbins)
+    gpu = charon_b200.GpuClassifier.from_references(refs, list(range(nbins)), bin_cat, len(cats))
+    try:
+        assert gpu.bin_size == idx.bin_size
+        for b, r in enumerate(refs):
+            assert int(gpu.hashes_per_bin[b]) == len(np.unique(oracle.minimisers(r))), b
+        assert np.array_equal(gpu.debug_dump_filter(), idx.rows())
+    finally:
+        gpu.close()

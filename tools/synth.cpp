@@ -18,7 +18,8 @@ void synth_reference(uint64_t seed, uint64_t n, char *out) {
     const uint64_t CH = 1 << 20;
 #pragma omp parallel for schedule(static)
     for (int64_t c = 0; c < int64_t((n + CH - 1) / CH); ++c) {
-        uint64_t s = seed * 0x9E3779B97F4A7C15ULL + uint64_t(c) * 0xD1B54A32D192ED03ULL + 1;
+        uint64_t s0 = seed ^ 0x5851F42D4C957F2DULL, s1 = uint64_t(c) + 0x14057B7EF767814FULL;
+        uint64_t s = splitmix64(s0) ^ (splitmix64(s1) * 0xD1B54A32D192ED03ULL);   // decorrelate seeds and chunks
         uint64_t lo = uint64_t(c) * CH, hi = lo + CH < n ? lo + CH : n;
         for (uint64_t i = lo; i < hi;) {
             uint64_t r = splitmix64(s);
