@@ -180,7 +180,9 @@ def test_sd_vector_payload_decoded_on_device(tmp_path, small):
         assert np.array_equal(g2.debug_dump_filter(), rows)
     finally:
         g2.close()
-    bad = high.copy(); bad[0] |= np.uint64(1) << np.uint64(63)     # an extra set bit must be rejected, not ignored
+    bad = high.copy()
+    z = int(np.flatnonzero(hb[:high_bits] == 0)[0])                 # an extra set bit must be rejected, not ignored
+    bad[z // 64] |= np.uint64(1) << np.uint64(z % 64)
     with pytest.raises(charon_b200.CharonGpuError):
         charon_b200.GpuClassifier(k=idx.k, w=idx.w, bins=idx.bins, bin_size=idx.bin_size, hash_funs=3, bin_to_cat=idx.bin_to_cat,
                                   ncat=idx.ncat, sd=(low, low_bits, bad, high_bits, wl))
