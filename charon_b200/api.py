@@ -61,7 +61,7 @@ class Info(C.Structure):
 
 EXPORTS = ["cg_create", "cg_build_index", "cg_destroy", "cg_last_error", "cg_set_stream", "cg_sync", "cg_set_model", "cg_count_batch", "cg_eval_batch",
            "cg_classify_batch", "cg_stage_batch", "cg_run_staged", "cg_fetch_staged", "cg_get_info", "cg_host_alloc", "cg_host_free", "cg_timer_start", "cg_timer_stop", "cg_debug_minimisers",
-           "cg_debug_query", "cg_debug_dump_filter"]
+           "cg_debug_query", "cg_debug_dump_filter", "cg_debug_force_generic"]
 
 _lib = None
 
@@ -97,6 +97,7 @@ def load_library():
     L.cg_debug_minimisers.argtypes = [vp, vp, u64, vp, u64, P(u64)]
     L.cg_debug_query.argtypes = [vp, vp, u64, vp]
     L.cg_debug_dump_filter.argtypes = [vp, vp]
+    L.cg_debug_force_generic.argtypes = [vp, i32]
     _lib = L
     return L
 
@@ -346,6 +347,9 @@ class GpuClassifier:
         out = np.zeros(cap, np.uint64); n = u64(0)
         self._check(self._L.cg_debug_minimisers(self._h, _ptr(a) if len(a) else None, len(a), out.ctypes.data, cap, C.byref(n)), "cg_debug_minimisers")
         return out[:n.value].copy()
+
+    def force_generic(self, on=True):
+        self._check(self._L.cg_debug_force_generic(self._h, 1 if on else 0), "cg_debug_force_generic")
 
     def debug_query(self, values) -> np.ndarray:
         v = np.ascontiguousarray(values, np.uint64)

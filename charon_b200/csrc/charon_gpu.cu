@@ -17,6 +17,7 @@
 #include <vector>
 
 #include "count_kernel.cuh"
+#include "count_kernel_v2.cuh"
 #include "eval_kernel.cuh"
 #include "filter_build.cuh"
 
@@ -72,6 +73,7 @@ struct cg_handle {
     bool staged_has_read_seg = false, staged_has_scalars = false;
     // launch config
     int grid_per_sm = 1;
+    bool force_generic = false;   // test hook: run the any-(k,w) kernel even when the specialised one applies
     // stats
     cg_info info{};
     // cg_timer_*: one outer event pair + three events per run recorded while timing
@@ -128,6 +130,27 @@ template <int MODE> cudaError_t launch_count_mode(cg_handle *h, const cgk::Count
     cgk::count_kernel<MODE><<<grid, cgk::NT, cgk::SMEM_BYTES, h->stream>>>(P);
     return cudaGetLastError();
 }
+// register-resident kernel for the (k, w) every `charon index` run produces by default (k=19, w=41)
+constexpr int FAST_K = 19, FAST_WV = 23;
+inline bool use_fast(const cg_handle *h) { return h->K == FAST_K && h->W - h->K + 1 == FAST_WV && !h->force_generic; }
+template <int MODE> cudaError_t launch_count_fast(cg_handle *h, const cgk::CountParams &P, int grid) {
+    using C = cgk::V2Cfg<FAST_K, FAST_WV>;
+    static bool attr_done[4] = {false, false, false, false};
+    if (!attr_done[MODE]) {
+        cudaError_t e = cudaFuncSetAttribute(cgk::count_kernel_v2<MODE, FAST_K, FAST_WV>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(C::SMEM));
+        if (e != cudaSuccess) return e;
+        attr_done[MODE] = true;
+    }
+    cgk::count_kernel_v2<MODE, FAST_K, FAST_WV><<<grid, cgk::NT2, C::SMEM, h->stream>>>(P);
+    return cudaGetLastError();
+}
+template <int MODE> int occupancy_fast() {
+    using C = cgk::V2Cfg<FAST_K, FAST_WV>;
+    int n = 0;
+    cudaFuncSetAttribute(cgk::count_kernel_v2<MODE, FAST_K, FAST_WV>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(C::SMEM));
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, cgk::count_kernel_v2<MODE, FAST_K, FAST_WV>, cgk::NT2, C::SMEM);
+    return n;
+}
 template <int MODE> int occupancy_mode() {
     int n = 0;
     cudaFuncSetAttribute(cgk::count_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(cgk::SMEM_BYTES));
@@ -140,6 +163,14 @@ int launch_count(cg_handle *h, const cgk::CountParams &P) {
     int grid = int(std::min<uint64_t>(uint64_t(h->sm_count) * h->grid_per_sm, P.n_reads));
     CU(h, cudaMemsetAsync(h->counter.p, 0, 4, h->stream));
     cudaError_t e;
+    if (use_fast(h)) {
+        switch (h->mode) {
+            case 0: e = launch_count_fast<0>(h, P, grid); break;
+            case 1: e = launch_count_fast<1>(h, P, grid); break;
+            case 2: e = launch_count_fast<2>(h, P, grid); break;
+            default: e = launch_count_fast<3>(h, P, grid); break;
+        }
+    } else
     switch (h->mode) {
         case 0: e = launch_count_mode<0>(h, P, grid); break;
         case 1: e = launch_count_mode<1>(h, P, grid); break;

@@ -1,0 +1,416 @@
+// charon_b200/csrc/count_kernel_v2.cuh — register-resident fused hot-path kernel, compile-time (k, w).
+//
+// Same contract as count_kernel.cuh (the generic any-(k,w) kernel) but specialised so that the inner loops are
+// fully unrolled and the k-mer values of a thread never leave its registers:
+//   * thread b of a 128-thread CTA owns block b = WW consecutive k-mers of the tile (WW = w-k+1 = 23);
+//   * phase 1: 41 base codes -> rolling canonical hash (two 32-bit limbs per strand, exact /5 by modular inverse)
+//              -> v[0..22] in registers, running prefix minimum -> shared memory (only array the neighbours read);
+//   * phase 2: descending suffix minimum from registers, combined with the right neighbour's prefix minimum
+//              = minimum of every window (van Herk / Gil-Werman), VALUES only;
+//   * emission rule (exact restatement of seqan3's stateful minimiser_view): with p(w) the tracked
+//              position,  p(w) = p(w-1) if min(w) == min(w-1) and p(w-1) is still inside window w, else the
+//              rightmost argmin of window w; a value is emitted whenever p changes.  When no window of the tile
+//              attains its minimum twice, that is simply "min(w) != min(w-1)" — the fast path.  Possible double
+//              minima are detected conservatively (equal low words in any of the three min steps); such tiles are
+//              re-done exactly by walking, per run of equal window minima, the chain p -> rightmost-argmin(p+1).
+//   * phase 3: emitted values -> 3 row gathers -> AND -> counting (identical to the generic kernel).
+// Tiles overlap by one window: local window 0 of a non-first tile is context only (the previous tile's last window).
+#pragma once
+#include "count_kernel.cuh"
+
+namespace cgk {
+
+constexpr int NT2 = 128;
+constexpr int LIST_CAP = 1024;
+constexpr uint64_t VMAX = ~0ull;   // never a real value: k <= 26 keeps the top 3 bits of v equal to the seed's (100b)
+
+constexpr uint32_t cpow5(int e) { uint32_t r = 1; for (int i = 0; i < e; ++i) r *= 5u; return r; }
+
+template <int KK, int WW> struct V2Cfg {
+    static constexpr int KL = KK < 13 ? KK : 13;
+    static constexpr int KH = KK - KL;
+    static constexpr uint32_t P_LO_TOP = cpow5(KL - 1);
+    static constexpr uint32_t P_HI_TOP = KH ? cpow5(KH - 1) : 0u;
+    static constexpr uint32_t P_KL = cpow5(KL);
+    static constexpr int NK = NT2 * WW;           // k-mers per tile
+    static constexpr int TW = (NT2 - 1) * WW;     // windows per tile (incl. the context window)
+    static constexpr int NB = NK + KK - 1;        // bases per tile
+    static constexpr int NCODE = WW + KK;         // codes per thread: one extra k-mer to the left (window k0-1)
+    static constexpr size_t SMEM = size_t(NK) * 8 + size_t(LIST_CAP) * 8 + (NB + 96) + 256 + 256 * 4 * 2 + 256 * 8 + 256 + 4 * 8;
+};
+
+struct Smem2 {
+    uint64_t *arr;      // NK: prefix minima (fast path) / raw values (exact path)
+    uint64_t *list;     // LIST_CAP emitted minimiser values
+    uint32_t *cnt, *uniq;
+    unsigned long long *best, *bestmask;
+    uint8_t *codes;     // 32 bytes of left slack + NB + slack ; codes[i] for tile base i lives at codes[32 + i]
+    uint8_t *lut, *b2c;
+};
+
+template <int KK, int WW>
+__device__ __forceinline__ Smem2 carve2(unsigned char *raw) {
+    using C = V2Cfg<KK, WW>;
+    Smem2 s;
+    s.arr = reinterpret_cast<uint64_t *>(raw);
+    s.list = s.arr + C::NK;
+    s.best = reinterpret_cast<unsigned long long *>(s.list + LIST_CAP);
+    s.bestmask = s.best + 256;
+    s.cnt = reinterpret_cast<uint32_t *>(s.bestmask + 4);
+    s.uniq = s.cnt + 256;
+    s.lut = reinterpret_cast<uint8_t *>(s.uniq + 256);
+    s.b2c = s.lut + 256;
+    s.codes = s.b2c + 256;
+    return s;
+}
+
+__device__ __forceinline__ uint32_t lo32(uint64_t x) { return uint32_t(x); }
+__device__ __forceinline__ uint64_t umin64(uint64_t a, uint64_t b) { return a < b ? a : b; }
+
+// per-read counters shared by the list phase and the inline (exact path) emission
+template <int MODE>
+struct Tally {
+    static constexpr int NW = ModeTraits<MODE>::NW;
+    uint32_t rc_cnt[4], rc_unq[4];
+    __device__ __forceinline__ void zero() {
+#pragma unroll
+        for (int b = 0; b < 4; ++b) { rc_cnt[b] = 0; rc_unq[b] = 0; }
+    }
+    __device__ __forceinline__ void add(const Mask<NW> &m, const unsigned long long *bm, bool small_bins, bool do_tot, bool do_unq,
+                                        const Smem2 &S) {
+        if (small_bins) {
+            const uint32_t m0 = uint32_t(m.w[0]);
+            if (do_tot) {
+#pragma unroll
+                for (int b = 0; b < 4; ++b) rc_cnt[b] += (m0 >> b) & 1u;
+            }
+            if (do_unq) {
+                const uint32_t mm = m0 & uint32_t(bm[0]);
+#pragma unroll
+                for (int b = 0; b < 4; ++b) rc_unq[b] += (mm == (1u << b)) ? 1u : 0u;
+            }
+        } else {
+            int pc = 0, ub = -1;
+#pragma unroll
+            for (int j = 0; j < NW; ++j) {
+                uint64_t x = m.w[j];
+                const uint64_t y = x & bm[j];
+                if (do_unq && y) { pc += __popcll(y); ub = j * 64 + (__ffsll((long long)y) - 1); }
+                if (do_tot)
+                    while (x) { const int b = __ffsll((long long)x) - 1; x &= x - 1; atomicAdd(&S.cnt[j * 64 + b], 1u); }
+            }
+            if (do_unq && pc == 1) atomicAdd(&S.uniq[S.b2c[ub]], 1u);
+        }
+    }
+};
+
+// rightmost argmin of arr[w .. w+WW-1] (exact path)
+template <int WW>
+__device__ __forceinline__ void scan_window(const uint64_t *arr, uint32_t w, uint64_t &m, uint32_t &r) {
+    m = arr[w]; r = w;
+#pragma unroll
+    for (int j = 1; j < WW; ++j) {
+        const uint64_t x = arr[w + j];
+        if (x <= m) { m = x; r = w + j; }
+    }
+}
+
+// One emitted minimiser handled on the spot (exact path / short segments): capture, query, count with shared-memory
+// atomics (the register tallies of the list phase are flushed into the same counters at the end of the read).
+template <int MODE>
+__device__ __noinline__ void process_exact(const CountParams &P, const Smem2 &S, uint32_t *s_nhash, uint64_t hv, bool do_tot, bool do_unq) {
+    constexpr int NW = ModeTraits<MODE>::NW;
+    if (P.dbg_out && do_tot) {
+        const unsigned long long slot = atomicAdd(P.dbg_n, 1ull);
+        if (slot < P.dbg_cap) P.dbg_out[slot] = hv;
+    }
+    if (do_tot) atomicAdd(s_nhash, 1u);
+    if (!P.filter) return;
+    const Mask<NW> m = bulk_contains<MODE>(P, hv);
+    int pc = 0, ub = -1;
+#pragma unroll
+    for (int j = 0; j < NW; ++j) {
+        uint64_t x = m.w[j];
+        const uint64_t y = x & S.bestmask[j];
+        if (do_unq && y) { pc += __popcll(y); ub = j * 64 + (__ffsll((long long)y) - 1); }
+        if (do_tot)
+            while (x) { const int b = __ffsll((long long)x) - 1; x &= x - 1; atomicAdd(&S.cnt[j * 64 + b], 1u); }
+    }
+    if (do_unq && pc == 1) atomicAdd(&S.uniq[S.b2c[ub]], 1u);
+}
+
+// Exact minimiser emission for one tile whose raw values sit in S.arr: per run of equal window minima walk the chain
+// p -> rightmost-argmin(window p+1) (see the file header).  `carry` = tracked position (tile-local) entering the tile.
+template <int MODE, int WW>
+__device__ __noinline__ void exact_tile(const CountParams &P, const Smem2 &S, uint32_t *s_nhash, long long *s_carry_pos, uint32_t *s_carry_valid,
+                                        uint32_t Tw, bool first, long long carry, uint64_t g0, bool do_tot, bool do_unq) {
+    for (uint32_t w = threadIdx.x; w < Tw; w += NT2) {
+        uint64_t m; uint32_t p;
+        scan_window<WW>(S.arr, w, m, p);
+        bool walk = false, emit = false;
+        if (w == 0) {
+            walk = true;
+            if (first) emit = true;
+            else if (carry >= 0 && carry < WW && S.arr[carry] == m) p = uint32_t(carry);   // context window: restore, no emission
+        } else {
+            uint64_t mp; uint32_t rp;
+            scan_window<WW>(S.arr, w - 1, mp, rp);
+            if (mp != m) { emit = true; walk = true; }
+        }
+        while (walk) {
+            if (emit) process_exact<MODE>(P, S, s_nhash, m, do_tot, do_unq);
+            const uint32_t nw = p + 1;
+            if (nw >= Tw) { *s_carry_pos = (long long)g0 + p; *s_carry_valid = 1; break; }
+            uint64_t m2; uint32_t r2;
+            scan_window<WW>(S.arr, nw, m2, r2);
+            if (m2 != m) break;
+            p = r2;
+            emit = true;
+        }
+    }
+}
+
+template <int MODE, int KK, int WW>
+__global__ void __launch_bounds__(NT2, 4) count_kernel_v2(const CountParams P) {
+    using C = V2Cfg<KK, WW>;
+    constexpr int NW = ModeTraits<MODE>::NW;
+    constexpr int KL = C::KL, KH = C::KH;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const Smem2 S = carve2<KK, WW>(smem_raw);
+    __shared__ uint32_t s_read, s_nlist, s_nhash, s_carry_valid;
+    __shared__ long long s_carry_pos;
+    __shared__ unsigned long long s_dbg_base;
+
+    const uint32_t tid = threadIdx.x, lane = tid & 31u;
+    const bool small_bins = (NW == 1) && (P.bins <= 4);
+    const uint64_t seed = P.seed;
+    for (uint32_t i = tid; i < 256; i += NT2) { S.lut[i] = base_code(i); S.b2c[i] = P.bin_to_cat[i]; }
+
+    Tally<MODE> T;
+
+    for (;;) {
+        __syncthreads();
+        if (tid == 0) s_read = atomicAdd(P.work_counter, 1u);
+        __syncthreads();
+        const uint32_t r = s_read;
+        if (r >= P.n_reads) break;
+        for (uint32_t i = tid; i < 256; i += NT2) { S.cnt[i] = 0; S.uniq[i] = 0; S.best[i] = 0; }
+        if (tid < 4) S.bestmask[tid] = P.single_pass ? ~0ull : 0ull;
+        if (tid == 0) s_nhash = 0;
+        T.zero();
+        const uint32_t seg0 = P.read_seg ? P.read_seg[r] : r;
+        const uint32_t seg1 = P.read_seg ? P.read_seg[r + 1] : r + 1;
+        const int npass = P.single_pass ? 1 : 2;
+
+        for (int pass = 0; pass < npass; ++pass) {
+            const bool do_tot = (pass == 0);
+            const bool do_unq = P.single_pass || pass == 1;
+            __syncthreads();
+            unsigned long long bm[NW];
+#pragma unroll
+            for (int j = 0; j < NW; ++j) bm[j] = S.bestmask[j];
+
+            for (uint32_t seg = seg0; seg < seg1; ++seg) {
+                const uint64_t sbase = P.seg_off[seg];
+                const uint64_t slen = P.seg_len ? P.seg_len[seg] : P.seg_off[seg + 1] - sbase;
+                if (slen < KK) continue;
+                const uint64_t nkm = slen - KK + 1;
+                if (nkm < WW) {
+                    // ---- fewer k-mers than one window: a single window, a single emission (its minimum) ----
+                    if (tid < 32) {
+                        uint64_t best = VMAX;
+                        for (uint32_t i = lane; i < nkm; i += 32) {
+                            uint64_t f = 0, rc = 0;
+                            for (int j = 0; j < KK; ++j) {
+                                const uint32_t c = S.lut[P.bases[sbase + i + j]];
+                                f = f * 5u + (c & 15u);
+                            }
+                            for (int j = KK; j-- > 0;) rc = rc * 5u + (S.lut[P.bases[sbase + i + j]] >> 4);
+                            best = umin64(best, umin64(f ^ seed, rc ^ seed));
+                        }
+#pragma unroll
+                        for (int o = 16; o > 0; o >>= 1) best = umin64(best, __shfl_xor_sync(0xFFFFFFFFu, best, o));
+                        if (lane == 0) process_exact<MODE>(P, S, &s_nhash, best, do_tot, do_unq);
+                    }
+                    continue;
+                }
+                const uint64_t nwin = nkm - WW + 1;
+                uint64_t g0 = 0;
+                bool first = true;
+                for (;;) {
+                    const uint32_t Tw = uint32_t(nwin - g0 < uint64_t(C::TW) ? nwin - g0 : uint64_t(C::TW));
+                    const uint32_t nk = Tw + WW - 1;
+                    const uint32_t nb = nk + KK - 1;
+                    // ---- phase 0: load + encode (codes[32 + i] = code of tile base i) ------------------------
+                    {
+                        const uint8_t *src = P.bases + sbase + g0;
+                        for (uint32_t i = tid; i < nb; i += NT2) S.codes[32 + i] = S.lut[src[i]];
+                    }
+                    __syncthreads();
+                    if (tid == 0) s_nlist = 0;
+                    // ---- phase 1: hash own block (+ the k-mer left of it), prefix minima -> smem ---------------
+                    const uint32_t k0 = tid * WW;
+                    const bool active = k0 < nk;
+                    const bool full = (k0 + WW <= nk);
+                    uint64_t v[WW];
+                    uint64_t vleft = VMAX;          // value of k-mer k0-1 (exists when k0 > 0)
+                    uint64_t m_prevwin = VMAX;      // minimum of window k0-1
+                    bool tie = false;
+                    if (active) {
+                        const uint8_t *cp = S.codes + 32 + k0 - 1;   // cp[t] = code of base k0-1+t, t = 0..NCODE-1
+                        uint32_t Hi = 0, Lo = 0, RHi = 0, RLo = 0;
+                        // k-mer k0-1 (garbage for k0 == 0: reads the zeroed slack, never used)
+#pragma unroll
+                        for (int j = 0; j < KH; ++j) Hi = Hi * 5u + (cp[j] & 15u);
+#pragma unroll
+                        for (int j = KH; j < KK; ++j) Lo = Lo * 5u + (cp[j] & 15u);
+#pragma unroll
+                        for (int j = KL; j-- > 0;) RLo = RLo * 5u + (cp[j] >> 4);
+#pragma unroll
+                        for (int j = KK; j-- > KL;) RHi = RHi * 5u + (cp[j] >> 4);
+                        {
+                            const uint64_t f = (uint64_t(Hi) * C::P_KL + Lo) ^ seed, rc = (uint64_t(RHi) * C::P_KL + RLo) ^ seed;
+                            vleft = k0 > 0 ? umin64(f, rc) : VMAX;
+                        }
+#pragma unroll
+                        for (int j = 0; j < WW; ++j) {
+                            // roll from k-mer (k0-1+j) to (k0+j): outgoing base cp[j], incoming cp[j+KK]
+                            const uint32_t b0 = cp[j], bh = cp[j + KH], bl = cp[j + KL], bK = cp[j + KK];
+                            Lo = (Lo - (bh & 15u) * C::P_LO_TOP) * 5u + (bK & 15u);
+                            RLo = (RLo - (b0 >> 4)) * INV5 + (bl >> 4) * C::P_LO_TOP;
+                            if (KH) {
+                                Hi = (Hi - (b0 & 15u) * C::P_HI_TOP) * 5u + (bh & 15u);
+                                RHi = (RHi - (bl >> 4)) * INV5 + (bK >> 4) * C::P_HI_TOP;
+                            }
+                            const uint64_t f = (uint64_t(Hi) * C::P_KL + Lo) ^ seed, rc = (uint64_t(RHi) * C::P_KL + RLo) ^ seed;
+                            v[j] = umin64(f, rc);
+                        }
+                        if (!full) {
+#pragma unroll
+                            for (int j = 0; j < WW; ++j) if (k0 + j >= nk) v[j] = VMAX;
+                        }
+                        uint64_t pm = v[0];
+                        S.arr[k0] = pm;
+#pragma unroll
+                        for (int j = 1; j < WW; ++j) {
+                            if (j == WW - 1) {   // window k0-1 = {k-mer k0-1} U prefix[0..WW-2]
+                                tie |= (lo32(vleft) == lo32(pm));
+                                m_prevwin = umin64(vleft, pm);
+                            }
+                            tie |= (lo32(v[j]) == lo32(pm)) && (full || k0 + j < nk);
+                            pm = umin64(pm, v[j]);
+                            S.arr[k0 + j] = pm;
+                        }
+                        if (WW == 1) m_prevwin = vleft;
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < WW; ++j) v[j] = VMAX;
+                    }
+                    __syncthreads();
+                    // ---- phase 2: suffix minima + neighbour prefix = window minima; emit on change -------------
+                    if (active && k0 < Tw) {
+                        const bool interior = (k0 + 2 * WW - 1 <= nk) && (k0 + WW <= Tw);   // every window of the block is valid
+                        uint64_t sv = VMAX, mw_next = 0;
+#pragma unroll
+                        for (int j = WW - 1; j >= 0; --j) {
+                            const uint32_t w = k0 + j;
+                            const bool wv = interior || (w < Tw);
+                            if (j < WW - 1) tie |= (lo32(v[j]) == lo32(sv));   // only full blocks get here: every v[j] is real
+                            sv = umin64(sv, v[j]);
+                            uint64_t mw = sv;
+                            if (j >= 1) {
+                                const uint64_t npm = wv ? S.arr[k0 + WW + j - 1] : VMAX;
+                                tie |= (lo32(npm) == lo32(sv)) && wv;
+                                mw = umin64(sv, npm);
+                            }
+                            // the element that just left (k-mer w-1) equal to the new minimum: an equal value W apart —
+                            // not a double minimum of any window, yet the tracked position moves without a value change
+                            tie |= (lo32(j >= 1 ? v[j >= 1 ? j - 1 : 0] : vleft) == lo32(mw)) && wv;
+                            if (j < WW - 1) {
+                                // window w+1 is a run start iff its minimum differs from window w's
+                                if (mw_next != mw && (interior || (w + 1 < Tw))) {
+                                    const uint32_t slot = atomicAdd(&s_nlist, 1u);
+                                    if (slot < LIST_CAP) S.list[slot] = mw_next;
+                                }
+                            }
+                            mw_next = mw;
+                        }
+                        // window k0 against window k0-1 (computed locally, no neighbour needed)
+                        if (k0 > 0) {
+                            if (mw_next != m_prevwin) {
+                                const uint32_t slot = atomicAdd(&s_nlist, 1u);
+                                if (slot < LIST_CAP) S.list[slot] = mw_next;
+                            }
+                        } else if (first) {
+                            const uint32_t slot = atomicAdd(&s_nlist, 1u);
+                            if (slot < LIST_CAP) S.list[slot] = mw_next;
+                        }
+                    }
+                    const int redo = __syncthreads_or(int(tie));
+                    uint32_t nl = s_nlist;
+                    if (redo || nl > LIST_CAP) {
+                        // ---- exact path: raw values to smem, per-run chain walk, inline emission -------------------
+                        const long long carry = s_carry_valid ? s_carry_pos - (long long)g0 : -1;   // read before anyone rewrites it
+                        if (active) {
+#pragma unroll
+                            for (int j = 0; j < WW; ++j) S.arr[k0 + j] = v[j];
+                        }
+                        __syncthreads();
+                        exact_tile<MODE, WW>(P, S, &s_nhash, &s_carry_pos, &s_carry_valid, Tw, first, carry, g0, do_tot, do_unq);
+                        nl = 0;
+                        __syncthreads();
+                    } else if (tid == 0) {
+                        s_carry_valid = 0;
+                    }
+                    // ---- phase 3: membership query + counting over the emission list -------------------------
+                    if (P.dbg_out && do_tot && nl) {
+                        if (tid == 0) s_dbg_base = atomicAdd(P.dbg_n, (unsigned long long)nl);
+                        __syncthreads();
+                        for (uint32_t i = tid; i < nl; i += NT2) {
+                            const unsigned long long slot = s_dbg_base + i;
+                            if (slot < P.dbg_cap) P.dbg_out[slot] = S.list[i];
+                        }
+                    }
+                    if (P.filter)
+                        for (uint32_t i = tid; i < nl; i += NT2) {
+                            const Mask<NW> m = bulk_contains<MODE>(P, S.list[i]);
+                            T.add(m, bm, small_bins, do_tot, do_unq, S);
+                        }
+                    if (tid == 0 && do_tot) atomicAdd(&s_nhash, nl);
+                    if (g0 + Tw >= nwin) break;
+                    g0 += Tw - 1;
+                    first = false;   // no barrier needed: the next tile's writes to codes/arr/list are all behind its own barriers
+                }  // tiles
+            }      // segments
+
+            if (small_bins) {
+#pragma unroll
+                for (int b = 0; b < 4; ++b) {
+                    const uint32_t c = __reduce_add_sync(0xFFFFFFFFu, T.rc_cnt[b]);
+                    const uint32_t u = __reduce_add_sync(0xFFFFFFFFu, T.rc_unq[b]);
+                    if (lane == 0) { if (c) atomicAdd(&S.cnt[b], c); if (u) atomicAdd(&S.uniq[S.b2c[b]], u); }
+                    T.rc_cnt[b] = 0; T.rc_unq[b] = 0;
+                }
+            }
+            __syncthreads();
+            if (do_tot) {
+                for (uint32_t b = tid; b < P.bins; b += NT2)
+                    atomicMax(&S.best[S.b2c[b]], ((unsigned long long)S.cnt[b] << 8) | (255ull - b));
+                __syncthreads();
+                if (!P.single_pass)
+                    for (uint32_t c = tid; c < P.ncat; c += NT2) {
+                        const uint32_t bb = 255u - uint32_t(S.best[c] & 255ull);
+                        if (bb < P.bins) atomicOr(&S.bestmask[bb >> 6], 1ull << (bb & 63u));
+                    }
+            }
+        }  // passes
+        __syncthreads();
+        if (tid == 0) P.num_hashes[r] = s_nhash;
+        for (uint32_t c = tid; c < P.ncat; c += NT2) {
+            P.counts[size_t(r) * P.ncat + c] = uint32_t(S.best[c] >> 8);
+            P.unique_counts[size_t(r) * P.ncat + c] = S.uniq[c];
+        }
+    }
+}
+
+}  // namespace cgk

@@ -203,6 +203,8 @@ int cg_get_info(cg_handle *h, cg_info *out);
 int cg_debug_minimisers(cg_handle *h, const char *bases, uint64_t len, uint64_t *out, uint64_t cap, uint64_t *n_out);
 /* bulk_contains for n hash values: masks[n * bin_words] in the seqan3 binning_bitvector word layout. */
 int cg_debug_query(cg_handle *h, const uint64_t *values, uint64_t n, uint64_t *masks);
+/* Run the generic any-(k,w) kernel even where the (k=19,w=41) specialisation applies (both are parity-tested). */
+int cg_debug_force_generic(cg_handle *h, int on);
 /* Copy the compacted filter back expanded to the plain row layout (bin_size * bin_words words). */
 int cg_debug_dump_filter(cg_handle *h, uint64_t *rows_out);
 

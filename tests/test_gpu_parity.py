@@ -204,3 +204,28 @@ def test_index_built_on_gpu_equals_oracle_index(nbins, lens):
         assert np.array_equal(gpu.debug_dump_filter(), idx.rows())
     finally:
         gpu.close()
+
+
+def test_generic_kernel_still_matches(small):
+    """The any-(k,w) kernel stays parity-green on the default (19, 41) when forced (it is the fallback for other k/w)."""
+    idx, refs, gpu = small
+    gpu.force_generic(True)
+    try:
+        for s in _tie_heavy_cases():
+            assert np.array_equal(gpu.debug_minimisers(s), np.sort(oracle.minimisers(s))), len(s)
+        bases, seg_off, _ = common.fixed_length_batch(15, refs, [0.45, 0.45], 500, 5000)
+        common.assert_parity(gpu.count_batch(bases, seg_off), idx.classify_batch(bases, seg_off))
+    finally:
+        gpu.force_generic(False)
+
+
+def test_equal_values_exactly_one_window_apart(small):
+    """Two equal minima exactly W k-mers apart never share a window, yet the tracked minimiser must be re-emitted
+    (seqan3 recomputes when the old one falls out).  Periodic sequences of period 23 create exactly that."""
+    idx, refs, gpu = small
+    rng = random.Random(5)
+    for period in (23, 46, 22, 24, 41):
+        unit = "".join(rng.choice("ACGT") for _ in range(period))
+        for n in (200, 3000, 7000):
+            s = (unit * (n // period + 2))[:n]
+            assert np.array_equal(gpu.debug_minimisers(s), np.sort(oracle.minimisers(s))), (period, n)
