@@ -51,14 +51,28 @@ __constant__ uint64_t c_ibf_seeds[5] = {13572355802537770549ULL, 130438178253327
 
 template <int NW> struct Mask { uint64_t w[NW]; };
 
-__device__ __forceinline__ uint32_t ldg_na_u32(const uint32_t *p) {
-    uint32_t v; asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(v) : "l"(p)); return v;
+// L2 residency control: filter rows are the hot, randomly re-referenced working set (evict_last), read bases are
+// touched exactly once (evict_first) — otherwise the 1 B/base stream pushes the filter out of the L2.
+__device__ __forceinline__ uint64_t l2_policy_evict_last() {
+    uint64_t p; asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(p)); return p;
 }
-__device__ __forceinline__ uint64_t ldg_na_u64(const uint64_t *p) {
-    uint64_t v; asm volatile("ld.global.nc.L1::no_allocate.u64 %0, [%1];" : "=l"(v) : "l"(p)); return v;
+__device__ __forceinline__ uint64_t l2_policy_evict_first() {
+    uint64_t p; asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p)); return p;
 }
-__device__ __forceinline__ void ldg_na_v2u64(const uint64_t *p, uint64_t &a, uint64_t &b) {
-    asm volatile("ld.global.nc.L1::no_allocate.v2.u64 {%0, %1}, [%2];" : "=l"(a), "=l"(b) : "l"(p));
+__device__ __forceinline__ uint32_t ldg_na_u32(const uint32_t *p, uint64_t pol) {
+    uint32_t v; asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.u32 %0, [%1], %2;" : "=r"(v) : "l"(p), "l"(pol)); return v;
+}
+__device__ __forceinline__ uint64_t ldg_na_u64(const uint64_t *p, uint64_t pol) {
+    uint64_t v; asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.u64 %0, [%1], %2;" : "=l"(v) : "l"(p), "l"(pol)); return v;
+}
+__device__ __forceinline__ void ldg_na_v2u64(const uint64_t *p, uint64_t &a, uint64_t &b, uint64_t pol) {
+    asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v2.u64 {%0, %1}, [%2], %3;" : "=l"(a), "=l"(b) : "l"(p), "l"(pol));
+}
+__device__ __forceinline__ uint4 ldg_stream_v4(const uint4 *p, uint64_t pol) {
+    uint4 v;
+    asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.u32 {%0, %1, %2, %3}, [%4], %5;"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p), "l"(pol));
+    return v;
 }
 
 // seqan3 interleaved_bloom_filter::hash_and_fit without the final * technical_bins
@@ -77,27 +91,27 @@ template <> struct ModeTraits<2> { static constexpr int NW = 2; };
 template <> struct ModeTraits<3> { static constexpr int NW = 4; };
 
 template <int MODE>
-__device__ __forceinline__ Mask<ModeTraits<MODE>::NW> fetch_row(const void *filter, uint64_t row, uint32_t row_shift) {
+__device__ __forceinline__ Mask<ModeTraits<MODE>::NW> fetch_row(const void *filter, uint64_t row, uint32_t row_shift, uint64_t pol) {
     Mask<ModeTraits<MODE>::NW> m;
     if (MODE == 0) {
         uint64_t bit = row << row_shift;
-        uint32_t word = ldg_na_u32(reinterpret_cast<const uint32_t *>(filter) + (bit >> 5));
+        uint32_t word = ldg_na_u32(reinterpret_cast<const uint32_t *>(filter) + (bit >> 5), pol);
         uint32_t rb = 1u << row_shift;
         uint32_t msk = rb >= 32 ? 0xFFFFFFFFu : ((1u << rb) - 1u);
         m.w[0] = (word >> (uint32_t(bit) & 31u)) & msk;
     } else if (MODE == 1) {
-        m.w[0] = ldg_na_u64(reinterpret_cast<const uint64_t *>(filter) + row);
+        m.w[0] = ldg_na_u64(reinterpret_cast<const uint64_t *>(filter) + row, pol);
     } else if (MODE == 2) {
-        ldg_na_v2u64(reinterpret_cast<const uint64_t *>(filter) + row * 2, m.w[0], m.w[1]);
+        ldg_na_v2u64(reinterpret_cast<const uint64_t *>(filter) + row * 2, m.w[0], m.w[1], pol);
     } else {
-        ldg_na_v2u64(reinterpret_cast<const uint64_t *>(filter) + row * 4, m.w[0], m.w[1]);
-        ldg_na_v2u64(reinterpret_cast<const uint64_t *>(filter) + row * 4 + 2, m.w[2], m.w[3]);
+        ldg_na_v2u64(reinterpret_cast<const uint64_t *>(filter) + row * 4, m.w[0], m.w[1], pol);
+        ldg_na_v2u64(reinterpret_cast<const uint64_t *>(filter) + row * 4 + 2, m.w[2], m.w[3], pol);
     }
     return m;
 }
 
 template <int MODE>
-__device__ __forceinline__ Mask<ModeTraits<MODE>::NW> bulk_contains(const CountParams &P, uint64_t value) {
+__device__ __forceinline__ Mask<ModeTraits<MODE>::NW> bulk_contains(const CountParams &P, uint64_t value, uint64_t pol) {
     constexpr int NW = ModeTraits<MODE>::NW;
     Mask<NW> acc;
     uint64_t rows[5];
@@ -107,7 +121,7 @@ __device__ __forceinline__ Mask<ModeTraits<MODE>::NW> bulk_contains(const CountP
     Mask<NW> r[5];
 #pragma unroll
     for (int i = 0; i < 5; ++i)
-        if (i < int(P.hash_funs)) r[i] = fetch_row<MODE>(P.filter, rows[i], P.row_shift);   // all loads in flight before the AND
+        if (i < int(P.hash_funs)) r[i] = fetch_row<MODE>(P.filter, rows[i], P.row_shift, pol);   // all loads in flight before the AND
 #pragma unroll
     for (int j = 0; j < NW; ++j) acc.w[j] = ~uint64_t(0);
 #pragma unroll
@@ -172,6 +186,7 @@ __global__ void __launch_bounds__(NT) count_kernel(const CountParams P) {
     const uint32_t lane = tid & 31u;
     const uint32_t K = P.K, kl = P.kl, kh = P.kh;
     const bool small_bins = (NW == 1) && (P.bins <= 4);
+    const uint64_t pol_filter = l2_policy_evict_last();
 
     for (uint32_t i = tid; i < 256; i += NT) { S.lut[i] = base_code(i); S.b2c[i] = P.bin_to_cat[i]; }
 
@@ -343,7 +358,7 @@ __global__ void __launch_bounds__(NT) count_kernel(const CountParams P) {
                     if (P.filter)
                     for (uint32_t i = tid; i < nl; i += NT) {
                         const uint64_t hv = S.v[S.ppos[i]];
-                        const Mask<NW> m = bulk_contains<MODE>(P, hv);
+                        const Mask<NW> m = bulk_contains<MODE>(P, hv, pol_filter);
                         if (small_bins) {
                             const uint32_t m0 = uint32_t(m.w[0]);
                             if (do_tot) {

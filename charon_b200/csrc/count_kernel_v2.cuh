@@ -36,7 +36,7 @@ template <int KK, int WW> struct V2Cfg {
     static constexpr int TW = (NT2 - 1) * WW;     // windows per tile (incl. the context window)
     static constexpr int NB = NK + KK - 1;        // bases per tile
     static constexpr int NCODE = WW + KK;         // codes per thread: one extra k-mer to the left (window k0-1)
-    static constexpr size_t SMEM = size_t(NK) * 8 + size_t(LIST_CAP) * 8 + (NB + 96) + 256 + 256 * 4 * 2 + 256 * 8 + 256 + 4 * 8;
+    static constexpr size_t SMEM = size_t(NK) * 8 + size_t(LIST_CAP) * 8 + (NB + 128) + 256 + 256 * 4 * 2 + 256 * 8 + 256 + 4 * 8;
 };
 
 struct Smem2 {
@@ -65,6 +65,10 @@ __device__ __forceinline__ Smem2 carve2(unsigned char *raw) {
 }
 
 __device__ __forceinline__ uint32_t lo32(uint64_t x) { return uint32_t(x); }
+__device__ __forceinline__ uint32_t encode4(const uint8_t *lut, uint32_t w) {   // 4 ASCII bases -> 4 codes
+    return uint32_t(lut[w & 0xFFu]) | (uint32_t(lut[(w >> 8) & 0xFFu]) << 8) | (uint32_t(lut[(w >> 16) & 0xFFu]) << 16) |
+           (uint32_t(lut[w >> 24]) << 24);
+}
 __device__ __forceinline__ uint64_t umin64(uint64_t a, uint64_t b) { return a < b ? a : b; }
 
 // per-read counters shared by the list phase and the inline (exact path) emission
@@ -126,7 +130,7 @@ __device__ __noinline__ void process_exact(const CountParams &P, const Smem2 &S,
     }
     if (do_tot) atomicAdd(s_nhash, 1u);
     if (!P.filter) return;
-    const Mask<NW> m = bulk_contains<MODE>(P, hv);
+    const Mask<NW> m = bulk_contains<MODE>(P, hv, l2_policy_evict_last());
     int pc = 0, ub = -1;
 #pragma unroll
     for (int j = 0; j < NW; ++j) {
@@ -184,6 +188,7 @@ __global__ void __launch_bounds__(NT2, 4) count_kernel_v2(const CountParams P) {
     const uint32_t tid = threadIdx.x, lane = tid & 31u;
     const bool small_bins = (NW == 1) && (P.bins <= 4);
     const uint64_t seed = P.seed;
+    const uint64_t pol_filter = l2_policy_evict_last(), pol_stream = l2_policy_evict_first();
     for (uint32_t i = tid; i < 256; i += NT2) { S.lut[i] = base_code(i); S.b2c[i] = P.bin_to_cat[i]; }
 
     Tally<MODE> T;
@@ -241,10 +246,30 @@ __global__ void __launch_bounds__(NT2, 4) count_kernel_v2(const CountParams P) {
                     const uint32_t Tw = uint32_t(nwin - g0 < uint64_t(C::TW) ? nwin - g0 : uint64_t(C::TW));
                     const uint32_t nk = Tw + WW - 1;
                     const uint32_t nb = nk + KK - 1;
-                    // ---- phase 0: load + encode (codes[32 + i] = code of tile base i) ------------------------
+                    // ---- phase 0: load + encode.  16-byte vectors aligned in GLOBAL memory, all of a thread's loads in
+                    //      flight before the first use; codes[32 + head + i] = code of tile base i -----------------
+                    const uint8_t *gsrc = P.bases + sbase + g0;
+                    const uint32_t head = uint32_t(reinterpret_cast<uintptr_t>(gsrc) & 15u);
                     {
-                        const uint8_t *src = P.bases + sbase + g0;
-                        for (uint32_t i = tid; i < nb; i += NT2) S.codes[32 + i] = S.lut[src[i]];
+                        const uint4 *vsrc = reinterpret_cast<const uint4 *>(gsrc - head);
+                        const uint32_t nvec = (head + nb + 15u) >> 4;
+                        constexpr int NV = (C::NB + 15 + 15) / 16 / NT2 + 1;   // vectors per thread (2 for k=19, w=41)
+                        uint4 x[NV];
+#pragma unroll
+                        for (int q = 0; q < NV; ++q) {
+                            const uint32_t i = tid + q * NT2;
+                            if (i < nvec) x[q] = ldg_stream_v4(vsrc + i, pol_stream);
+                        }
+#pragma unroll
+                        for (int q = 0; q < NV; ++q) {
+                            const uint32_t i = tid + q * NT2;
+                            if (i < nvec) {
+                                uint4 y;
+                                y.x = encode4(S.lut, x[q].x); y.y = encode4(S.lut, x[q].y);
+                                y.z = encode4(S.lut, x[q].z); y.w = encode4(S.lut, x[q].w);
+                                *reinterpret_cast<uint4 *>(S.codes + 32 + 16 * i) = y;
+                            }
+                        }
                     }
                     __syncthreads();
                     if (tid == 0) s_nlist = 0;
@@ -257,7 +282,7 @@ __global__ void __launch_bounds__(NT2, 4) count_kernel_v2(const CountParams P) {
                     uint64_t m_prevwin = VMAX;      // minimum of window k0-1
                     bool tie = false;
                     if (active) {
-                        const uint8_t *cp = S.codes + 32 + k0 - 1;   // cp[t] = code of base k0-1+t, t = 0..NCODE-1
+                        const uint8_t *cp = S.codes + 32 + head + k0 - 1;   // cp[t] = code of base k0-1+t, t = 0..NCODE-1
                         uint32_t Hi = 0, Lo = 0, RHi = 0, RLo = 0;
                         // k-mer k0-1 (garbage for k0 == 0: reads the zeroed slack, never used)
 #pragma unroll
@@ -373,7 +398,7 @@ __global__ void __launch_bounds__(NT2, 4) count_kernel_v2(const CountParams P) {
                     }
                     if (P.filter)
                         for (uint32_t i = tid; i < nl; i += NT2) {
-                            const Mask<NW> m = bulk_contains<MODE>(P, S.list[i]);
+                            const Mask<NW> m = bulk_contains<MODE>(P, S.list[i], pol_filter);
                             T.add(m, bm, small_bins, do_tot, do_unq, S);
                         }
                     if (tid == 0 && do_tot) atomicAdd(&s_nhash, nl);

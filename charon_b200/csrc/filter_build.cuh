@@ -129,7 +129,7 @@ template <int MODE>
 __global__ void query_kernel(const CountParams P, const uint64_t *__restrict__ values, uint64_t n, uint32_t bin_words,
                              uint64_t *__restrict__ masks) {
     for (uint64_t i = blockIdx.x * uint64_t(blockDim.x) + threadIdx.x; i < n; i += uint64_t(gridDim.x) * blockDim.x) {
-        const auto m = bulk_contains<MODE>(P, values[i]);
+        const auto m = bulk_contains<MODE>(P, values[i], l2_policy_evict_last());
         for (uint32_t j = 0; j < bin_words; ++j) masks[i * bin_words + j] = m.w[j < ModeTraits<MODE>::NW ? j : 0];
     }
 }
