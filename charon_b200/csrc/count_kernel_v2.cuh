@@ -21,7 +21,8 @@
 namespace cgk {
 
 constexpr int NT2 = 128;
-constexpr int LIST_CAP = 1024;
+constexpr int LIST_CAP = 1024;   // compacted emission list of a tile (expected ~265 entries)
+constexpr int PRIV_CAP = 8;      // per-thread emission slots (expected ~2 per 23 windows); overrun => exact path
 constexpr uint64_t VMAX = ~0ull;   // never a real value: k <= 26 keeps the top 3 bits of v equal to the seed's (100b)
 
 constexpr uint32_t cpow5(int e) { uint32_t r = 1; for (int i = 0; i < e; ++i) r *= 5u; return r; }
@@ -36,11 +37,12 @@ template <int KK, int WW> struct V2Cfg {
     static constexpr int TW = (NT2 - 1) * WW;     // windows per tile (incl. the context window)
     static constexpr int NB = NK + KK - 1;        // bases per tile
     static constexpr int NCODE = WW + KK;         // codes per thread: one extra k-mer to the left (window k0-1)
-    static constexpr size_t SMEM = size_t(NK) * 8 + size_t(LIST_CAP) * 8 + (NB + 128) + 256 + 256 * 4 * 2 + 256 * 8 + 256 + 4 * 8;
+    static constexpr size_t SMEM = size_t(NK) * 8 + size_t(LIST_CAP) * 8 + size_t(NT2) * PRIV_CAP * 8 + (NB + 128) + 256 + 256 * 4 * 2 + 256 * 8 + 256 + 4 * 8;
 };
 
 struct Smem2 {
     uint64_t *arr;      // NK: prefix minima (fast path) / raw values (exact path)
+    uint64_t *priv;     // NT2 * PRIV_CAP per-thread emission slots (overrun spills into list: such tiles are redone)
     uint64_t *list;     // LIST_CAP emitted minimiser values
     uint32_t *cnt, *uniq;
     unsigned long long *best, *bestmask;
@@ -53,7 +55,8 @@ __device__ __forceinline__ Smem2 carve2(unsigned char *raw) {
     using C = V2Cfg<KK, WW>;
     Smem2 s;
     s.arr = reinterpret_cast<uint64_t *>(raw);
-    s.list = s.arr + C::NK;
+    s.priv = s.arr + C::NK;
+    s.list = s.priv + NT2 * PRIV_CAP;
     s.best = reinterpret_cast<unsigned long long *>(s.list + LIST_CAP);
     s.bestmask = s.best + 256;
     s.cnt = reinterpret_cast<uint32_t *>(s.bestmask + 4);
@@ -117,6 +120,36 @@ __device__ __forceinline__ void scan_window(const uint64_t *arr, uint32_t w, uin
         const uint64_t x = arr[w + j];
         if (x <= m) { m = x; r = w + j; }
     }
+}
+
+// Phase 2 for one full block.  v[] = the block's 23 values; on return v[0] holds the minimum of window k0.
+// next = prefix minima of the right neighbour block (shared memory).  EDGE: some windows of the block lie beyond Tw.
+// Emission: window w+1 starts a run iff min(w+1) != min(w).  `tie` collects every situation in which positions (not
+// just values) would matter: equal low words between the two operands of any min, or between the value that has just
+// left the window and the new minimum (an equal value exactly W k-mers apart).
+template <int WW, bool EDGE>
+__device__ __forceinline__ void p2_block(uint64_t (&v)[WW], uint64_t vleft, const uint64_t *next, uint32_t k0, uint32_t Tw, uint64_t *&pslot,
+                                         bool &tie) {
+    uint64_t sv = v[WW - 1], mw_next = 0;
+#pragma unroll
+    for (int j = WW - 1; j >= 0; --j) {
+        const bool wv = !EDGE || (k0 + j < Tw);
+        if (j < WW - 1) { tie = tie | (lo32(v[j]) == lo32(sv)); sv = umin64(sv, v[j]); }
+        uint64_t mw = sv;
+        if (j >= 1) {
+            const uint64_t npm = (EDGE && !wv) ? VMAX : next[j - 1];
+            tie = tie | ((lo32(npm) == lo32(sv)) & wv);
+            mw = umin64(sv, npm);
+        }
+        const uint64_t leaving = j >= 1 ? v[j >= 1 ? j - 1 : 0] : vleft;
+        tie = tie | ((lo32(leaving) == lo32(mw)) & wv);
+        if (j < WW - 1) {
+            const bool start = (mw_next != mw) & (!EDGE || (k0 + j + 1 < Tw));
+            if (start) { *pslot = mw_next; ++pslot; }
+        }
+        mw_next = mw;
+    }
+    v[0] = mw_next;
 }
 
 // One emitted minimiser handled on the spot (exact path / short segments): capture, query, count with shared-memory
@@ -319,10 +352,10 @@ __global__ void __launch_bounds__(NT2, 4) count_kernel_v2(const CountParams P) {
 #pragma unroll
                         for (int j = 1; j < WW; ++j) {
                             if (j == WW - 1) {   // window k0-1 = {k-mer k0-1} U prefix[0..WW-2]
-                                tie |= (lo32(vleft) == lo32(pm));
+                                tie = tie | (lo32(vleft) == lo32(pm));
                                 m_prevwin = umin64(vleft, pm);
                             }
-                            tie |= (lo32(v[j]) == lo32(pm)) && (full || k0 + j < nk);
+                            tie = tie | ((lo32(v[j]) == lo32(pm)) & (full || k0 + j < nk));
                             pm = umin64(pm, v[j]);
                             S.arr[k0 + j] = pm;
                         }
@@ -332,44 +365,29 @@ __global__ void __launch_bounds__(NT2, 4) count_kernel_v2(const CountParams P) {
                         for (int j = 0; j < WW; ++j) v[j] = VMAX;
                     }
                     __syncthreads();
-                    // ---- phase 2: suffix minima + neighbour prefix = window minima; emit on change -------------
+                    // ---- phase 2: suffix minima + neighbour prefix = window minima; a window whose minimum differs from
+                    //      its predecessor's starts a run = one emission, appended to the thread's private slots ----------
+                    const uint64_t v0_raw = v[0];
+                    uint64_t *pslot = S.priv + tid * PRIV_CAP;
+                    uint64_t *const pslot0 = pslot;
                     if (active && k0 < Tw) {
-                        const bool interior = (k0 + 2 * WW - 1 <= nk) && (k0 + WW <= Tw);   // every window of the block is valid
-                        uint64_t sv = VMAX, mw_next = 0;
+                        const bool interior = (k0 + WW <= Tw);   // every window of the block is valid (=> next block's prefix exists)
+                        if (interior) p2_block<WW, false>(v, vleft, S.arr + k0 + WW, k0, Tw, pslot, tie);
+                        else p2_block<WW, true>(v, vleft, S.arr + k0 + WW, k0, Tw, pslot, tie);
+                        // window k0 against window k0-1 (computed locally in phase 1, no neighbour needed); v[0] now holds min(k0)
+                        if (k0 > 0 ? (v[0] != m_prevwin) : first) { *pslot = v[0]; ++pslot; }
+                    }
+                    {   // compaction: warp scan of the per-thread counts, one shared atomic per warp
+                        const uint32_t cnt = uint32_t(pslot - pslot0);
+                        tie |= (cnt > PRIV_CAP);            // private slots overrun: redo the tile exactly (results below are discarded)
+                        uint32_t inc = cnt;
 #pragma unroll
-                        for (int j = WW - 1; j >= 0; --j) {
-                            const uint32_t w = k0 + j;
-                            const bool wv = interior || (w < Tw);
-                            if (j < WW - 1) tie |= (lo32(v[j]) == lo32(sv));   // only full blocks get here: every v[j] is real
-                            sv = umin64(sv, v[j]);
-                            uint64_t mw = sv;
-                            if (j >= 1) {
-                                const uint64_t npm = wv ? S.arr[k0 + WW + j - 1] : VMAX;
-                                tie |= (lo32(npm) == lo32(sv)) && wv;
-                                mw = umin64(sv, npm);
-                            }
-                            // the element that just left (k-mer w-1) equal to the new minimum: an equal value W apart —
-                            // not a double minimum of any window, yet the tracked position moves without a value change
-                            tie |= (lo32(j >= 1 ? v[j >= 1 ? j - 1 : 0] : vleft) == lo32(mw)) && wv;
-                            if (j < WW - 1) {
-                                // window w+1 is a run start iff its minimum differs from window w's
-                                if (mw_next != mw && (interior || (w + 1 < Tw))) {
-                                    const uint32_t slot = atomicAdd(&s_nlist, 1u);
-                                    if (slot < LIST_CAP) S.list[slot] = mw_next;
-                                }
-                            }
-                            mw_next = mw;
-                        }
-                        // window k0 against window k0-1 (computed locally, no neighbour needed)
-                        if (k0 > 0) {
-                            if (mw_next != m_prevwin) {
-                                const uint32_t slot = atomicAdd(&s_nlist, 1u);
-                                if (slot < LIST_CAP) S.list[slot] = mw_next;
-                            }
-                        } else if (first) {
-                            const uint32_t slot = atomicAdd(&s_nlist, 1u);
-                            if (slot < LIST_CAP) S.list[slot] = mw_next;
-                        }
+                        for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, inc, o); if (lane >= uint32_t(o)) inc += t; }
+                        uint32_t wbase = 0;
+                        if (lane == 31) wbase = atomicAdd(&s_nlist, inc);
+                        wbase = __shfl_sync(0xFFFFFFFFu, wbase, 31);
+                        uint32_t dst = wbase + inc - cnt;
+                        for (uint32_t q = 0; q < cnt && q < PRIV_CAP; ++q, ++dst) if (dst < LIST_CAP) S.list[dst] = pslot0[q];
                     }
                     const int redo = __syncthreads_or(int(tie));
                     uint32_t nl = s_nlist;
@@ -378,7 +396,7 @@ __global__ void __launch_bounds__(NT2, 4) count_kernel_v2(const CountParams P) {
                         const long long carry = s_carry_valid ? s_carry_pos - (long long)g0 : -1;   // read before anyone rewrites it
                         if (active) {
 #pragma unroll
-                            for (int j = 0; j < WW; ++j) S.arr[k0 + j] = v[j];
+                            for (int j = 0; j < WW; ++j) S.arr[k0 + j] = j == 0 ? v0_raw : v[j];
                         }
                         __syncthreads();
                         exact_tile<MODE, WW>(P, S, &s_nhash, &s_carry_pos, &s_carry_valid, Tw, first, carry, g0, do_tot, do_unq);
