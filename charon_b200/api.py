@@ -9,7 +9,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libcharon_gpu.so")
+LIB_PATH = os.environ.get("CHARON_GPU_LIB") or os.path.join(_HERE, "libcharon_gpu.so")   # env override: kernel-variant experiments
 
 u8, u16, u32, u64, i32, f32, f64, vp = C.c_uint8, C.c_uint16, C.c_uint32, C.c_uint64, C.c_int32, C.c_float, C.c_double, C.c_void_p
 
@@ -349,7 +349,9 @@ class GpuClassifier:
         return out[:n.value].copy()
 
     def force_generic(self, on=True):
-        self._check(self._L.cg_debug_force_generic(self._h, 1 if on else 0), "cg_debug_force_generic")
+        """0/False: default dispatch (warp-per-read + CTA-per-read for long reads); 1/True: generic any-(k,w) kernel;
+        2: CTA-per-read specialised kernel for every read."""
+        self._check(self._L.cg_debug_force_generic(self._h, int(on)), "cg_debug_force_generic")
 
     def debug_query(self, values) -> np.ndarray:
         v = np.ascontiguousarray(values, np.uint64)

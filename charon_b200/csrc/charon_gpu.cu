@@ -18,6 +18,7 @@
 
 #include "count_kernel.cuh"
 #include "count_kernel_v2.cuh"
+#include "count_kernel_v3.cuh"
 #include "eval_kernel.cuh"
 #include "filter_build.cuh"
 
@@ -73,6 +74,9 @@ struct cg_handle {
     bool staged_has_read_seg = false, staged_has_scalars = false;
     // launch config
     int grid_per_sm = 1;
+    int warp_grid_per_sm = 1;
+    uint64_t staged_max_read_len = 0;
+    bool force_cta = false;       // test hook: CTA-per-read kernel for every read
     bool force_generic = false;   // test hook: run the any-(k,w) kernel even when the specialised one applies
     // stats
     cg_info info{};
@@ -116,6 +120,7 @@ cgk::CountParams make_params(cg_handle *h) {
     P.num_hashes = h->num_hashes.as<uint32_t>(); P.counts = h->counts.as<uint32_t>(); P.unique_counts = h->unique.as<uint32_t>();
     P.work_counter = h->counter.as<uint32_t>();
     P.seg_len = nullptr;
+    P.long_read_min = 0; P.long_only = 0;
     P.dbg_out = nullptr; P.dbg_cap = 0; P.dbg_n = nullptr;
     return P;
 }
@@ -151,6 +156,26 @@ template <int MODE> int occupancy_fast() {
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, cgk::count_kernel_v2<MODE, FAST_K, FAST_WV>, cgk::NT2, C::SMEM);
     return n;
 }
+// warp-per-read kernel (count_kernel_v3): SMALL = at most 4 bins (register tallies, no per-warp counter arrays)
+constexpr unsigned long long LONG_READ_MIN = 65536;   // reads at least this long go to the CTA-per-read kernel
+template <int MODE, bool SMALL> cudaError_t launch_count_warp(cg_handle *h, const cgk::CountParams &P, int grid) {
+    using C = cgk::V3Cfg<FAST_K, FAST_WV, SMALL>;
+    static bool attr_done = false;
+    if (!attr_done) {
+        cudaError_t e = cudaFuncSetAttribute(cgk::count_kernel_v3<MODE, FAST_K, FAST_WV, SMALL>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(C::SMEM));
+        if (e != cudaSuccess) return e;
+        attr_done = true;
+    }
+    cgk::count_kernel_v3<MODE, FAST_K, FAST_WV, SMALL><<<grid, cgk::WARPS3 * 32, C::SMEM, h->stream>>>(P);
+    return cudaGetLastError();
+}
+template <int MODE, bool SMALL> int occupancy_warp() {
+    using C = cgk::V3Cfg<FAST_K, FAST_WV, SMALL>;
+    int n = 0;
+    cudaFuncSetAttribute(cgk::count_kernel_v3<MODE, FAST_K, FAST_WV, SMALL>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(C::SMEM));
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, cgk::count_kernel_v3<MODE, FAST_K, FAST_WV, SMALL>, cgk::WARPS3 * 32, C::SMEM);
+    return n;
+}
 template <int MODE> int occupancy_mode() {
     int n = 0;
     cudaFuncSetAttribute(cgk::count_kernel<MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(cgk::SMEM_BYTES));
@@ -163,7 +188,36 @@ int launch_count(cg_handle *h, const cgk::CountParams &P) {
     int grid = int(std::min<uint64_t>(uint64_t(h->sm_count) * h->grid_per_sm, P.n_reads));
     CU(h, cudaMemsetAsync(h->counter.p, 0, 4, h->stream));
     cudaError_t e;
-    if (use_fast(h)) {
+    if (use_fast(h) && !h->force_cta) {
+        // warp-per-read kernel for everything shorter than LONG_READ_MIN, then (only if needed) the CTA-per-read kernel
+        cgk::CountParams Q = P;
+        const bool dispatch = Q.seg_len == nullptr;          // index-build chunks are all handled by the warp kernel
+        Q.long_read_min = dispatch ? LONG_READ_MIN : 0;
+        const int wgrid = int(std::min<uint64_t>(uint64_t(h->sm_count) * h->warp_grid_per_sm, (uint64_t(P.n_reads) + cgk::WARPS3 - 1) / cgk::WARPS3));
+        const bool small = h->bins <= 4;
+        switch (h->mode) {
+            case 0: e = small ? launch_count_warp<0, true>(h, Q, wgrid) : launch_count_warp<0, false>(h, Q, wgrid); break;
+            case 1: e = launch_count_warp<1, false>(h, Q, wgrid); break;
+            case 2: e = launch_count_warp<2, false>(h, Q, wgrid); break;
+            default: e = launch_count_warp<3, false>(h, Q, wgrid); break;
+        }
+        h->info.count_grid = uint32_t(wgrid);
+        if (e == cudaSuccess && dispatch && h->staged_max_read_len >= LONG_READ_MIN) {
+            Q.long_only = 1;
+            e = cudaMemsetAsync(h->counter.p, 0, 4, h->stream);
+            if (e == cudaSuccess)
+                switch (h->mode) {
+                    case 0: e = launch_count_fast<0>(h, Q, grid); break;
+                    case 1: e = launch_count_fast<1>(h, Q, grid); break;
+                    case 2: e = launch_count_fast<2>(h, Q, grid); break;
+                    default: e = launch_count_fast<3>(h, Q, grid); break;
+                }
+            h->info.last_kernel_launches += 1;
+        }
+        if (e != cudaSuccess) return fail(h, CG_ERR_CUDA, "count kernel launch failed: %s", cudaGetErrorString(e));
+        h->info.last_kernel_launches += 1;
+        return 0;
+    } else if (use_fast(h)) {
         switch (h->mode) {
             case 0: e = launch_count_fast<0>(h, P, grid); break;
             case 1: e = launch_count_fast<1>(h, P, grid); break;
@@ -253,6 +307,11 @@ int stage(cg_handle *h, const cg_batch *b, const cg_read_scalars *sc) {
     }
     CU(h, cudaEventRecord(h->ev[1], h->stream));
     h->staged_reads = b->n_reads; h->staged_segs = b->n_segs; h->staged_bases = nbases; h->staged_has_read_seg = b->read_seg != nullptr;
+    h->staged_max_read_len = 0;
+    for (uint32_t r = 0; r < b->n_reads; ++r) {
+        const uint32_t s0 = b->read_seg ? b->read_seg[r] : r, s1 = b->read_seg ? b->read_seg[r + 1] : r + 1;
+        if (s1 > s0) h->staged_max_read_len = std::max<uint64_t>(h->staged_max_read_len, b->seg_off[s1] - b->seg_off[s0]);
+    }
     h->info.last_bases = nbases;
     return 0;
 }

@@ -39,6 +39,9 @@ struct CountParams {
     // outputs
     uint32_t *num_hashes, *counts, *unique_counts;
     uint32_t *work_counter;
+    // read-length dispatch between the warp-per-read and the CTA-per-read kernels (0 = no dispatch)
+    unsigned long long long_read_min;   // warp kernel skips reads with >= this many bases ...
+    uint32_t long_only;                 // ... and the CTA kernel, when set, processes only those
     // emission capture (index construction + test hook): emitted minimiser values appended to dbg_out;
     // filter == nullptr skips the membership query entirely (capture-only launch)
     uint64_t *dbg_out;

@@ -21,7 +21,13 @@
 namespace cgk {
 
 constexpr int NT2 = 128;
-constexpr int LIST_CAP = 1024;   // compacted emission list of a tile (expected ~265 entries)
+#ifndef CG_V2_MINB
+#define CG_V2_MINB 4
+#endif
+#ifndef CG_V2_LIST_CAP
+#define CG_V2_LIST_CAP 1024
+#endif
+constexpr int LIST_CAP = CG_V2_LIST_CAP;   // compacted emission list of a tile (expected ~265 entries)
 constexpr int PRIV_CAP = 8;      // per-thread emission slots (expected ~2 per 23 windows); overrun => exact path
 constexpr uint64_t VMAX = ~0ull;   // never a real value: k <= 26 keeps the top 3 bits of v equal to the seed's (100b)
 
@@ -180,8 +186,9 @@ __device__ __noinline__ void process_exact(const CountParams &P, const Smem2 &S,
 // p -> rightmost-argmin(window p+1) (see the file header).  `carry` = tracked position (tile-local) entering the tile.
 template <int MODE, int WW>
 __device__ __noinline__ void exact_tile(const CountParams &P, const Smem2 &S, uint32_t *s_nhash, long long *s_carry_pos, uint32_t *s_carry_valid,
-                                        uint32_t Tw, bool first, long long carry, uint64_t g0, bool do_tot, bool do_unq) {
-    for (uint32_t w = threadIdx.x; w < Tw; w += NT2) {
+                                        uint32_t Tw, bool first, long long carry, uint64_t g0, bool do_tot, bool do_unq,
+                                        uint32_t t0 = threadIdx.x, uint32_t stride = NT2) {
+    for (uint32_t w = t0; w < Tw; w += stride) {
         uint64_t m; uint32_t p;
         scan_window<WW>(S.arr, w, m, p);
         bool walk = false, emit = false;
@@ -197,7 +204,14 @@ __device__ __noinline__ void exact_tile(const CountParams &P, const Smem2 &S, ui
         while (walk) {
             if (emit) process_exact<MODE>(P, S, s_nhash, m, do_tot, do_unq);
             const uint32_t nw = p + 1;
-            if (nw >= Tw) { *s_carry_pos = (long long)g0 + p; *s_carry_valid = 1; break; }
+            if (nw >= Tw) {
+                // The chain leaves the tile.  Only the run that is still alive at the tile's last window owns the carried
+                // position (an earlier run whose tracked element merely sits near the tile end must not overwrite it).
+                uint64_t ml; uint32_t rl;
+                scan_window<WW>(S.arr, Tw - 1, ml, rl);
+                if (ml == m) { *s_carry_pos = (long long)g0 + p; *s_carry_valid = 1; }
+                break;
+            }
             uint64_t m2; uint32_t r2;
             scan_window<WW>(S.arr, nw, m2, r2);
             if (m2 != m) break;
@@ -208,7 +222,7 @@ __device__ __noinline__ void exact_tile(const CountParams &P, const Smem2 &S, ui
 }
 
 template <int MODE, int KK, int WW>
-__global__ void __launch_bounds__(NT2, 4) count_kernel_v2(const CountParams P) {
+__global__ void __launch_bounds__(NT2, CG_V2_MINB) count_kernel_v2(const CountParams P) {
     using C = V2Cfg<KK, WW>;
     constexpr int NW = ModeTraits<MODE>::NW;
     constexpr int KL = C::KL, KH = C::KH;
@@ -232,6 +246,11 @@ __global__ void __launch_bounds__(NT2, 4) count_kernel_v2(const CountParams P) {
         __syncthreads();
         const uint32_t r = s_read;
         if (r >= P.n_reads) break;
+        if (P.long_only) {   // companion launch of the warp-per-read kernel: only the reads it skipped
+            const uint32_t a = P.read_seg ? P.read_seg[r] : r, b = P.read_seg ? P.read_seg[r + 1] : r + 1;
+            const uint64_t total = b > a ? (P.seg_len ? P.seg_off[b - 1] + P.seg_len[b - 1] : P.seg_off[b]) - P.seg_off[a] : 0;
+            if (total < P.long_read_min) continue;
+        }
         for (uint32_t i = tid; i < 256; i += NT2) { S.cnt[i] = 0; S.uniq[i] = 0; S.best[i] = 0; }
         if (tid < 4) S.bestmask[tid] = P.single_pass ? ~0ull : 0ull;
         if (tid == 0) s_nhash = 0;
@@ -398,6 +417,8 @@ __global__ void __launch_bounds__(NT2, 4) count_kernel_v2(const CountParams P) {
 #pragma unroll
                             for (int j = 0; j < WW; ++j) S.arr[k0 + j] = j == 0 ? v0_raw : v[j];
                         }
+                        __syncthreads();
+                        if (tid == 0) s_carry_valid = 0;     // re-armed by the walker of the run alive at the last window
                         __syncthreads();
                         exact_tile<MODE, WW>(P, S, &s_nhash, &s_carry_pos, &s_carry_valid, Tw, first, carry, g0, do_tot, do_unq);
                         nl = 0;

@@ -1,0 +1,325 @@
+// charon_b200/csrc/count_kernel_v3.cuh — warp-per-read variant of the register-resident kernel (count_kernel_v2.cuh).
+//
+// Same arithmetic, same exactness argument, but the unit of work is a WARP: each warp owns one read at a time and walks
+// it in tiles of 31*23 = 713 windows, so there is no CTA-wide barrier anywhere on the hot path (only __syncwarp).  Warps
+// drift apart in phase, which lets one warp's load / gather latency hide behind the others' arithmetic, and the next
+// tile's bases are prefetched into registers (tagged by address) while the current tile is processed.
+// Reads longer than P.long_read_min are left to the CTA-per-read kernel (count_kernel_v2), launched afterwards on the
+// same stream, so that one very long read cannot serialise on a single warp.
+#pragma once
+#include "count_kernel_v2.cuh"
+
+namespace cgk {
+
+constexpr int WARPS3 = 4;              // warps per CTA (independent of each other)
+constexpr int WLIST_CAP = 256;         // compacted emission list of a warp tile (expected ~65 entries)
+
+template <int KK, int WW, bool SMALL> struct V3Cfg {
+    static constexpr int NK = 32 * WW;            // k-mers per warp tile
+    static constexpr int TW = 31 * WW;            // windows per warp tile (incl. the context window)
+    static constexpr int NB = NK + KK - 1;        // bases per warp tile
+    static constexpr int NVEC = (NB + 15 + 15) / 16;      // 16-byte vectors that can cover a tile at any alignment
+    static constexpr int NVL = (NVEC + 31) / 32;          // vectors per lane
+    static constexpr int NCNT = SMALL ? 8 : 256;
+    static constexpr int CODES = ((32 + 16 * NVL * 32 + 64) + 15) / 16 * 16;
+    static constexpr size_t WARP_BYTES = size_t(NK) * 8 + size_t(32) * PRIV_CAP * 8 + size_t(WLIST_CAP) * 8 + size_t(NCNT) * 8 + 32 +
+                                         size_t(NCNT) * 4 * 2 + CODES;
+    static constexpr size_t SMEM = 512 + WARPS3 * WARP_BYTES;
+};
+
+template <int MODE, int KK, int WW, bool SMALL>
+__global__ void __launch_bounds__(WARPS3 * 32, 4) count_kernel_v3(const CountParams P) {
+    using C2 = V2Cfg<KK, WW>;
+    using C = V3Cfg<KK, WW, SMALL>;
+    constexpr int NW = ModeTraits<MODE>::NW;
+    constexpr int KL = C2::KL, KH = C2::KH;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+    Smem2 S;
+    S.lut = smem_raw;
+    S.b2c = smem_raw + 256;
+    {
+        unsigned char *w = smem_raw + 512 + size_t(warp) * C::WARP_BYTES;
+        S.arr = reinterpret_cast<uint64_t *>(w);
+        S.priv = S.arr + C::NK;
+        S.list = S.priv + 32 * PRIV_CAP;
+        S.best = reinterpret_cast<unsigned long long *>(S.list + WLIST_CAP);
+        S.bestmask = S.best + C::NCNT;
+        S.cnt = reinterpret_cast<uint32_t *>(S.bestmask + 4);
+        S.uniq = S.cnt + C::NCNT;
+        S.codes = reinterpret_cast<uint8_t *>(S.uniq + C::NCNT);
+    }
+    __shared__ uint32_t s_nhash_w[WARPS3], s_carry_valid_w[WARPS3];
+    __shared__ long long s_carry_pos_w[WARPS3];
+    uint32_t *const s_nhash = &s_nhash_w[warp];
+    uint32_t *const s_carry_valid = &s_carry_valid_w[warp];
+    long long *const s_carry_pos = &s_carry_pos_w[warp];
+
+    const bool small_bins = SMALL;
+    const uint64_t seed = P.seed;
+    const uint64_t pol_filter = l2_policy_evict_last(), pol_stream = l2_policy_evict_first();
+    for (uint32_t i = tid; i < 256; i += WARPS3 * 32) { S.lut[i] = base_code(i); S.b2c[i] = P.bin_to_cat[i]; }
+    __syncthreads();   // the only CTA-wide barrier
+
+    auto ticket = [&]() -> uint32_t {
+        uint32_t t = 0;
+        if (lane == 0) t = atomicAdd(P.work_counter, 1u);
+        return __shfl_sync(0xFFFFFFFFu, t, 0);
+    };
+    // prefetched vectors of the next tile, tagged by their (16-byte aligned) global address
+    uint4 pf[C::NVL];
+    const uint8_t *pf_addr = nullptr;
+    auto prefetch = [&](const uint8_t *gsrc, uint32_t nb) {
+        const uint32_t head = uint32_t(reinterpret_cast<uintptr_t>(gsrc) & 15u);
+        const uint4 *vsrc = reinterpret_cast<const uint4 *>(gsrc - head);
+        const uint32_t nvec = (head + nb + 15u) >> 4;
+#pragma unroll
+        for (int q = 0; q < C::NVL; ++q) {
+            const uint32_t i = lane + q * 32;
+            if (i < nvec) pf[q] = ldg_stream_v4(vsrc + i, pol_stream);
+        }
+        pf_addr = gsrc;
+    };
+
+    Tally<MODE> T;
+    uint32_t cur = ticket();
+    uint32_t nxt = ticket();
+    while (cur < P.n_reads) {
+        const uint32_t r = cur;
+        const uint32_t seg0 = P.read_seg ? P.read_seg[r] : r;
+        const uint32_t seg1 = P.read_seg ? P.read_seg[r + 1] : r + 1;
+        // address of the first tile of the next read (prefetch target while this read's last tile is processed)
+        const uint8_t *next_read_src = nullptr;
+        uint32_t next_read_nb = 0;
+        if (nxt < P.n_reads) {
+            const uint32_t ns = P.read_seg ? P.read_seg[nxt] : nxt;
+            const uint64_t nbase = P.seg_off[ns];
+            const uint64_t nlen = P.seg_len ? P.seg_len[ns] : P.seg_off[ns + 1] - nbase;
+            if (nlen >= uint64_t(KK + WW - 1)) {
+                const uint64_t nwin = nlen - KK + 1 - WW + 1;
+                const uint32_t tw = uint32_t(nwin < uint64_t(C::TW) ? nwin : uint64_t(C::TW));
+                next_read_src = P.bases + nbase;
+                next_read_nb = tw + WW - 1 + KK - 1;
+            }
+        }
+        bool skip = false;
+        if (P.long_read_min) {   // long reads are left to the CTA-per-read kernel
+            const uint64_t total = (P.seg_len ? P.seg_off[seg1 - 1] + P.seg_len[seg1 - 1] : P.seg_off[seg1]) - P.seg_off[seg0];
+            skip = seg1 > seg0 && total >= P.long_read_min;
+        }
+        if (!skip) {
+        for (uint32_t i = lane; i < uint32_t(C::NCNT); i += 32) { S.cnt[i] = 0; S.uniq[i] = 0; S.best[i] = 0; }
+        if (lane < 4) S.bestmask[lane] = P.single_pass ? ~0ull : 0ull;
+        if (lane == 0) *s_nhash = 0;
+        T.zero();
+        __syncwarp();
+        const int npass = P.single_pass ? 1 : 2;
+        for (int pass = 0; pass < npass; ++pass) {
+            const bool do_tot = (pass == 0);
+            const bool do_unq = P.single_pass || pass == 1;
+            __syncwarp();
+            unsigned long long bm[NW];
+#pragma unroll
+            for (int j = 0; j < NW; ++j) bm[j] = S.bestmask[j];
+            const bool last_pass = (pass == npass - 1);
+
+            for (uint32_t seg = seg0; seg < seg1; ++seg) {
+                const uint64_t sbase = P.seg_off[seg];
+                const uint64_t slen = P.seg_len ? P.seg_len[seg] : P.seg_off[seg + 1] - sbase;
+                if (slen < KK) continue;
+                const uint64_t nkm = slen - KK + 1;
+                if (nkm < WW) {   // a single window: its minimum is the only emission
+                    uint64_t best = VMAX;
+                    for (uint32_t i = lane; i < nkm; i += 32) {
+                        uint64_t f = 0, rc = 0;
+                        for (int j = 0; j < KK; ++j) f = f * 5u + (S.lut[P.bases[sbase + i + j]] & 15u);
+                        for (int j = KK; j-- > 0;) rc = rc * 5u + (S.lut[P.bases[sbase + i + j]] >> 4);
+                        best = umin64(best, umin64(f ^ seed, rc ^ seed));
+                    }
+#pragma unroll
+                    for (int o = 16; o > 0; o >>= 1) best = umin64(best, __shfl_xor_sync(0xFFFFFFFFu, best, o));
+                    if (lane == 0) process_exact<MODE>(P, S, s_nhash, best, do_tot, do_unq);
+                    __syncwarp();
+                    continue;
+                }
+                const uint64_t nwin = nkm - WW + 1;
+                uint64_t g0 = 0;
+                bool first = true;
+                for (;;) {
+                    const uint32_t Tw = uint32_t(nwin - g0 < uint64_t(C::TW) ? nwin - g0 : uint64_t(C::TW));
+                    const uint32_t nk = Tw + WW - 1;
+                    const uint32_t nb = nk + KK - 1;
+                    const bool last_tile = (g0 + Tw >= nwin);
+                    // ---- phase 0: (prefetched) 16-byte vectors -> code bytes in shared memory -----------------------
+                    const uint8_t *gsrc = P.bases + sbase + g0;
+                    const uint32_t head = uint32_t(reinterpret_cast<uintptr_t>(gsrc) & 15u);
+                    const uint32_t nvec = (head + nb + 15u) >> 4;
+                    if (pf_addr != gsrc) prefetch(gsrc, nb);          // not predicted: load now
+                    __syncwarp();                                      // previous tile's readers of codes are done
+#pragma unroll
+                    for (int q = 0; q < C::NVL; ++q) {
+                        const uint32_t i = lane + q * 32;
+                        if (i < nvec) {
+                            uint4 y;
+                            y.x = encode4(S.lut, pf[q].x); y.y = encode4(S.lut, pf[q].y);
+                            y.z = encode4(S.lut, pf[q].z); y.w = encode4(S.lut, pf[q].w);
+                            *reinterpret_cast<uint4 *>(S.codes + 32 + 16 * i) = y;
+                        }
+                    }
+                    // predict + prefetch the next tile: next tile of this segment, else the next read's first tile
+                    if (!last_tile) {
+                        const uint64_t g1 = g0 + Tw - 1;
+                        const uint32_t tw1 = uint32_t(nwin - g1 < uint64_t(C::TW) ? nwin - g1 : uint64_t(C::TW));
+                        prefetch(P.bases + sbase + g1, tw1 + WW - 1 + KK - 1);
+                    } else if (last_pass && seg + 1 == seg1 && next_read_src) {
+                        prefetch(next_read_src, next_read_nb);
+                    } else pf_addr = nullptr;
+                    __syncwarp();
+                    // ---- phase 1: rolling canonical hash of the lane's block, prefix minima -> smem -------------------
+                    const uint32_t k0 = lane * WW;
+                    const bool active = k0 < nk;
+                    const bool full = (k0 + WW <= nk);
+                    uint64_t v[WW];
+                    uint64_t vleft = VMAX, m_prevwin = VMAX;
+                    bool tie = false;
+                    if (active) {
+                        const uint8_t *cp = S.codes + 32 + head + k0 - 1;
+                        uint32_t Hi = 0, Lo = 0, RHi = 0, RLo = 0;
+#pragma unroll
+                        for (int j = 0; j < KH; ++j) Hi = Hi * 5u + (cp[j] & 15u);
+#pragma unroll
+                        for (int j = KH; j < KK; ++j) Lo = Lo * 5u + (cp[j] & 15u);
+#pragma unroll
+                        for (int j = KL; j-- > 0;) RLo = RLo * 5u + (cp[j] >> 4);
+#pragma unroll
+                        for (int j = KK; j-- > KL;) RHi = RHi * 5u + (cp[j] >> 4);
+                        {
+                            const uint64_t f = (uint64_t(Hi) * C2::P_KL + Lo) ^ seed, rc = (uint64_t(RHi) * C2::P_KL + RLo) ^ seed;
+                            vleft = k0 > 0 ? umin64(f, rc) : VMAX;
+                        }
+#pragma unroll
+                        for (int j = 0; j < WW; ++j) {
+                            const uint32_t b0 = cp[j], bh = cp[j + KH], bl = cp[j + KL], bK = cp[j + KK];
+                            Lo = (Lo - (bh & 15u) * C2::P_LO_TOP) * 5u + (bK & 15u);
+                            RLo = (RLo - (b0 >> 4)) * INV5 + (bl >> 4) * C2::P_LO_TOP;
+                            if (KH) {
+                                Hi = (Hi - (b0 & 15u) * C2::P_HI_TOP) * 5u + (bh & 15u);
+                                RHi = (RHi - (bl >> 4)) * INV5 + (bK >> 4) * C2::P_HI_TOP;
+                            }
+                            const uint64_t f = (uint64_t(Hi) * C2::P_KL + Lo) ^ seed, rc = (uint64_t(RHi) * C2::P_KL + RLo) ^ seed;
+                            v[j] = umin64(f, rc);
+                        }
+                        if (!full) {
+#pragma unroll
+                            for (int j = 0; j < WW; ++j) if (k0 + j >= nk) v[j] = VMAX;
+                        }
+                        uint64_t pm = v[0];
+                        S.arr[k0] = pm;
+#pragma unroll
+                        for (int j = 1; j < WW; ++j) {
+                            if (j == WW - 1) {
+                                tie = tie | (lo32(vleft) == lo32(pm));
+                                m_prevwin = umin64(vleft, pm);
+                            }
+                            tie = tie | ((lo32(v[j]) == lo32(pm)) & (full || k0 + j < nk));
+                            pm = umin64(pm, v[j]);
+                            S.arr[k0 + j] = pm;
+                        }
+                        if (WW == 1) m_prevwin = vleft;
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < WW; ++j) v[j] = VMAX;
+                    }
+                    __syncwarp();
+                    // ---- phase 2: window minima, run starts -> private slots -> warp-compacted list -------------------
+                    const uint64_t v0_raw = v[0];
+                    uint64_t *pslot = S.priv + lane * PRIV_CAP;
+                    uint64_t *const pslot0 = pslot;
+                    if (active && k0 < Tw) {
+                        if (k0 + WW <= Tw) p2_block<WW, false>(v, vleft, S.arr + k0 + WW, k0, Tw, pslot, tie);
+                        else p2_block<WW, true>(v, vleft, S.arr + k0 + WW, k0, Tw, pslot, tie);
+                        if (k0 > 0 ? (v[0] != m_prevwin) : first) { *pslot = v[0]; ++pslot; }
+                    }
+                    const uint32_t cnt = uint32_t(pslot - pslot0);
+                    tie = tie | (cnt > PRIV_CAP);
+#ifdef CG_FORCE_EXACT
+                    tie = true;
+#endif
+                    uint32_t inc = cnt;
+#pragma unroll
+                    for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, inc, o); if (lane >= uint32_t(o)) inc += t; }
+                    uint32_t nl = __shfl_sync(0xFFFFFFFFu, inc, 31);
+                    const bool redo = __any_sync(0xFFFFFFFFu, tie) || nl > WLIST_CAP;
+                    if (!redo) {
+                        uint32_t dst = inc - cnt;
+                        for (uint32_t q = 0; q < cnt; ++q, ++dst) S.list[dst] = pslot0[q];
+                        if (lane == 0) *s_carry_valid = 0;
+                    } else {
+                        // ---- exact path: raw values to smem, per-run chain walk, inline emission ------------------------
+                        const long long carry = *s_carry_valid ? *s_carry_pos - (long long)g0 : -1;
+                        __syncwarp();
+                        if (active) {
+#pragma unroll
+                            for (int j = 0; j < WW; ++j) S.arr[k0 + j] = j == 0 ? v0_raw : v[j];
+                        }
+                        __syncwarp();
+                        if (lane == 0) *s_carry_valid = 0;   // re-armed by the walker of the run alive at the last window
+                        __syncwarp();
+                        exact_tile<MODE, WW>(P, S, s_nhash, s_carry_pos, s_carry_valid, Tw, first, carry, g0, do_tot, do_unq, lane, 32u);
+                        nl = 0;
+                    }
+                    __syncwarp();
+                    // ---- phase 3: membership query + counting ----------------------------------------------------------
+                    if (P.dbg_out && do_tot && nl) {
+                        unsigned long long base = 0;
+                        if (lane == 0) base = atomicAdd(P.dbg_n, (unsigned long long)nl);
+                        base = __shfl_sync(0xFFFFFFFFu, base, 0);
+                        for (uint32_t i = lane; i < nl; i += 32) if (base + i < P.dbg_cap) P.dbg_out[base + i] = S.list[i];
+                    }
+                    if (P.filter)
+                        for (uint32_t i = lane; i < nl; i += 32) {
+                            const Mask<NW> m = bulk_contains<MODE>(P, S.list[i], pol_filter);
+                            T.add(m, bm, small_bins, do_tot, do_unq, S);
+                        }
+                    if (lane == 0 && do_tot && nl) atomicAdd(s_nhash, nl);
+                    if (last_tile) break;
+                    g0 += Tw - 1;
+                    first = false;
+                }  // tiles
+            }      // segments
+
+            if (small_bins) {
+#pragma unroll
+                for (int b = 0; b < 4; ++b) {
+                    const uint32_t c = __reduce_add_sync(0xFFFFFFFFu, T.rc_cnt[b]);
+                    const uint32_t u = __reduce_add_sync(0xFFFFFFFFu, T.rc_unq[b]);
+                    if (lane == 0) { if (c) atomicAdd(&S.cnt[b], c); if (u) atomicAdd(&S.uniq[S.b2c[b]], u); }
+                    T.rc_cnt[b] = 0; T.rc_unq[b] = 0;
+                }
+            }
+            __syncwarp();
+            if (do_tot) {
+                for (uint32_t b = lane; b < P.bins; b += 32)
+                    atomicMax(&S.best[S.b2c[b]], ((unsigned long long)S.cnt[b] << 8) | (255ull - b));
+                __syncwarp();
+                if (!P.single_pass)
+                    for (uint32_t c = lane; c < P.ncat; c += 32) {
+                        const uint32_t bb = 255u - uint32_t(S.best[c] & 255ull);
+                        if (bb < P.bins) atomicOr(&S.bestmask[bb >> 6], 1ull << (bb & 63u));
+                    }
+            }
+        }  // passes
+        __syncwarp();
+        if (lane == 0) P.num_hashes[r] = *s_nhash;
+        for (uint32_t c = lane; c < P.ncat; c += 32) {
+            P.counts[size_t(r) * P.ncat + c] = uint32_t(S.best[c] >> 8);
+            P.unique_counts[size_t(r) * P.ncat + c] = S.uniq[c];
+        }
+        __syncwarp();
+        }  // !skip
+        cur = nxt;
+        nxt = ticket();
+    }
+}
+
+}  // namespace cgk

@@ -64,6 +64,25 @@ def test_long_read_tiling(small):
     assert np.array_equal(gpu.debug_minimisers(s), np.sort(oracle.minimisers(s)))
 
 
+def test_mixed_lengths_dispatch_between_warp_and_cta_kernels(small):
+    """Reads shorter than 65 536 bases run on the warp-per-read kernel, longer ones on the CTA-per-read kernel of the
+    same batch; both must agree with the oracle (incl. a read exactly at the threshold and a low-complexity long read)."""
+    idx, refs, gpu = small
+    rng = np.random.default_rng(21)
+    lens = [100, 8000, 65_535, 65_536, 65_537, 120_000, 30, 5000, 250_000, 713 + 40, 714 + 40, 1426 + 40]
+    pieces = []
+    for ln in lens:
+        st = int(rng.integers(0, 300_000 - ln)) if ln < 300_000 else 0
+        pieces.append(refs[int(rng.integers(0, 2))][st:st + ln].copy())
+    pieces.append(np.frombuffer((b"ACGTTGCA" * 20000)[:100_001], np.uint8))
+    bases, seg_off = common.ragged_batch(rng, pieces)
+    n = len(pieces)
+    mq, cr = common.scalars(n)
+    want = idx.classify_batch(bases, seg_off, mean_q=mq, compression=cr)
+    got = gpu.classify_batch(bases, seg_off, mq, cr, np.diff(seg_off).astype(np.uint32))
+    common.assert_parity(got, want)
+
+
 def test_counts_and_calls_dehost_config1_like(small):
     idx, refs, gpu = small
     n, L = 2000, 5000
@@ -206,10 +225,12 @@ def test_index_built_on_gpu_equals_oracle_index(nbins, lens):
         gpu.close()
 
 
-def test_generic_kernel_still_matches(small):
-    """The any-(k,w) kernel stays parity-green on the default (19, 41) when forced (it is the fallback for other k/w)."""
+@pytest.mark.parametrize("which", [1, 2])
+def test_other_kernels_still_match(small, which):
+    """The any-(k,w) kernel (1) and the CTA-per-read specialised kernel (2: used for long reads) stay parity-green on the
+    default (19, 41) when forced for every read."""
     idx, refs, gpu = small
-    gpu.force_generic(True)
+    gpu.force_generic(which)
     try:
         for s in _tie_heavy_cases():
             assert np.array_equal(gpu.debug_minimisers(s), np.sort(oracle.minimisers(s))), len(s)
@@ -229,3 +250,21 @@ def test_equal_values_exactly_one_window_apart(small):
         for n in (200, 3000, 7000):
             s = (unit * (n // period + 2))[:n]
             assert np.array_equal(gpu.debug_minimisers(s), np.sort(oracle.minimisers(s))), (period, n)
+
+
+def test_tie_run_crossing_a_tile_boundary_regression(small):
+    """Golden regression (tests/golden/tie_tile_boundary_809.txt): a run of equal window minima crosses the 713-window
+    warp tile while an EARLIER run's tracked element also sits past the tile end — only the run alive at the last window
+    may hand its position to the next tile.  Also shifted so the same structure meets the 2921-window CTA tile."""
+    import os
+    idx, refs, gpu = small
+    t = open(os.path.join(os.path.dirname(__file__), "golden", "tie_tile_boundary_809.txt")).read().strip()
+    rng = random.Random(3)
+    for mode in (0, 2, 1):
+        gpu.force_generic(mode)
+        try:
+            for pad in (0, 2921 - 713, 1, 5, 712, 2208 + 713):
+                s = "".join(rng.choice("ACGT") for _ in range(pad)) + t
+                assert np.array_equal(gpu.debug_minimisers(s), np.sort(oracle.minimisers(s))), (mode, pad)
+        finally:
+            gpu.force_generic(0)
