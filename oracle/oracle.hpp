@@ -303,6 +303,27 @@ struct TrainingData {  // classify_stats.hpp:34-114
     bool add_neg(float v) { if (neg.size() < num_reads_to_fit && v > 0) neg.push_back(v); else check_status(); return complete; }
 };
 
+// mean / variance helpers and the moment fits (classify_stats.hpp:20-31,127-141,171-190)
+template <class V> inline double mean_d(const V &v) { double s = 0.0; for (auto x : v) s += x; return v.empty() ? 0 : s / double(v.size()); }
+inline double variance_d(const std::vector<float> &v, double mean) {   // the reference's lambda takes a FLOAT accumulator
+    double acc = 0.0;
+    for (float val : v) { const float a = float(acc); acc = double(a) + ((double(val) - mean) * (double(val) - mean)); }
+    return v.size() <= 1 ? 0 : acc / double(v.size() - 1);
+}
+inline void fit_gamma(float *g, const std::vector<float> &data) {
+    const double mu = mean_d(data), ln_mu = std::log(mu);
+    std::vector<float> logs(data.size());
+    for (size_t i = 0; i < data.size(); ++i) logs[i] = std::log(data[i]);
+    const double s = ln_mu - mean_d(logs);
+    g[0] = float((3 - s + std::sqrt((s - 3) * (s - 3) + 24 * s)) / (12 * s));
+    g[2] = float(mu / g[0]);
+}
+inline void fit_beta(float *b, const std::vector<float> &data) {
+    const double mu = mean_d(data), var = variance_d(data, mu);
+    b[0] = float(mu * ((mu * (1 - mu) / var) - 1));
+    b[1] = float((1 - mu) * ((mu * (1 - mu) / var) - 1));
+}
+
 struct StatsModel {  // classify_stats.hpp:395-584
     bool ready_ = false;
     Options opt;
@@ -321,7 +342,14 @@ struct StatsModel {  // classify_stats.hpp:395-584
             if (t.pos_complete) m.k_pos.fit(t.pos);
             if (t.neg_complete) m.k_neg.fit(t.neg);
         }
-        // beta / gamma re-fits (:289-339) are not modelled: defaults kept (only reachable with --extract).
+        else if (m.dist == "beta") {   // train_beta :315-339, BetaParams::fit :171-190
+            if (t.pos_complete) fit_beta(m.b_pos, t.pos);
+            if (t.neg_complete) fit_beta(m.b_neg, t.neg);
+        } else {                       // train_gamma :289-313, GammaParams::fit :127-136, fit_loc :138-141
+            if (t.pos_complete) fit_gamma(m.g_pos, t.pos);
+            if (t.neg_complete) fit_gamma(m.g_neg, t.neg);
+            else m.g_neg[1] = float(mean_d(t.neg) - double(m.g_neg[0] * m.g_neg[2]));   // NB: also on the default path (empty data -> loc = -shape*scale)
+        }
         m.ready = true; t.pos.clear(); t.neg.clear();
     }
     void force_ready() { for (size_t i = 0; i < models.size(); ++i) if (!models[i].ready) train(i); ready_ = true; }
