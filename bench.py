@@ -167,6 +167,14 @@ def run_b200(args, wl):
     t0 = time.time()
     gpu = charon_b200.GpuClassifier.from_references(records, rec_bin, [0, 1], 2, device=local_rank)   # index built on the GPU
     build_s = time.time() - t0
+    partitioned = bool(args.partitioned and world > 1)
+    if partitioned:
+        # BASELINE config 4: the filter is split by row range over the ranks; rows owned by a peer are fetched through its
+        # NVLink peer mapping inside the count kernel.  Reads stay sharded, still no data-path collective.
+        import torch
+        from charon_b200 import multi
+        gpu.partition(rank, world)
+        multi.exchange_partitions(gpu, dist, rank, world, device=torch.device("cuda", local_rank))
     gpu.set_model(charon_b200.DehostOptions(), host_index=0)
     # this rank's batch (weak scaling: R reads per GPU per step), in pinned host memory
     bases = pinned_array((R * L,), np.uint8)
@@ -252,7 +260,8 @@ def run_b200(args, wl):
     line = {"metric": "reads_per_sec", "value": value, "unit": "reads/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": total_ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64",
             "data": "synthetic",
-            "config": {"workload": wl["desc"], "reads_per_step_per_gpu": R, "read_len": L, "k": 19, "w": 41, "hash_funs": 3,
+            "config": {"workload": wl["desc"] + (" -- filter PARTITIONED by row range across the GPUs (NVLink peer gathers)" if partitioned else ""),
+                       "filter_partitioned": partitioned, "reads_per_step_per_gpu": R, "read_len": L, "k": 19, "w": 41, "hash_funs": 3,
                        "filter_rows": int(info.bin_size), "filter_bytes_hbm": int(info.filter_bytes), "row_bits": int(info.row_bits),
                        "minimisers_per_step_per_gpu": minimisers, "classified_frac": float((res["call"] != 255).mean()),
                        "l2_note": "step input (1 B/base x reads) is larger than the 126 MB L2 and is re-read every step; no flush needed",
@@ -293,6 +302,7 @@ def main():
     ap.add_argument("--workload", default="bacterial", choices=sorted(WORKLOADS))
     ap.add_argument("--reads-per-step", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--partitioned", action="store_true", help="N>1: split the filter by row range across the GPUs instead of replicating it")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     wl = WORKLOADS[args.workload]

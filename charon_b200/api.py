@@ -61,7 +61,8 @@ class Info(C.Structure):
 
 EXPORTS = ["cg_create", "cg_build_index", "cg_destroy", "cg_last_error", "cg_set_stream", "cg_sync", "cg_set_model", "cg_count_batch", "cg_eval_batch",
            "cg_classify_batch", "cg_stage_batch", "cg_run_staged", "cg_fetch_staged", "cg_get_info", "cg_host_alloc", "cg_host_free", "cg_timer_start", "cg_timer_stop", "cg_debug_minimisers",
-           "cg_debug_query", "cg_debug_dump_filter", "cg_debug_force_generic"]
+           "cg_debug_query", "cg_debug_dump_filter", "cg_debug_force_generic", "cg_create_partitioned", "cg_partition_from_replicated",
+           "cg_partition_export", "cg_partition_attach_ipc", "cg_partition_attach_peer"]
 
 _lib = None
 
@@ -78,6 +79,11 @@ def load_library():
     P = C.POINTER
     L.cg_create.argtypes = [i32, P(IndexDesc), C.c_size_t, P(vp)]
     L.cg_build_index.argtypes = [i32, P(BuildDesc), C.c_size_t, vp, P(vp)]
+    L.cg_create_partitioned.argtypes = [i32, P(IndexDesc), u32, u32, P(vp)]
+    L.cg_partition_from_replicated.argtypes = [vp, u32, u32]
+    L.cg_partition_export.argtypes = [vp, vp]
+    L.cg_partition_attach_ipc.argtypes = [vp, u32, vp]
+    L.cg_partition_attach_peer.argtypes = [vp, u32, vp]
     L.cg_destroy.argtypes = [vp]; L.cg_destroy.restype = None
     L.cg_last_error.argtypes = [vp]; L.cg_last_error.restype = C.c_char_p
     L.cg_set_stream.argtypes = [vp, vp]
@@ -187,7 +193,9 @@ class GpuClassifier:
         self.bin_size = int(self.info().bin_size)
         return self
 
-    def __init__(self, *, k, w, bins, bin_size, hash_funs, bin_to_cat, ncat, rows=None, sd=None, device=0, mem_budget=0):
+    def __init__(self, *, k, w, bins, bin_size, hash_funs, bin_to_cat, ncat, rows=None, sd=None, device=0, mem_budget=0, part=None):
+        """part=(rank, world): store only this rank's row range of the filter (cg_create_partitioned); the other parts must
+        then be attached (attach_peer / attach_ipc) before the first batch."""
         L = load_library()
         self._L = L
         self.k, self.w, self.bins, self.bin_size, self.ncat = k, w, bins, bin_size, ncat
@@ -211,11 +219,30 @@ class GpuClassifier:
         d.ncat, d.bin_to_cat = ncat, b2c.ctypes.data
         self._keep.append(b2c)
         h = vp()
-        rc = L.cg_create(device, C.byref(d), mem_budget, C.byref(h))
+        if part is not None:
+            rc = L.cg_create_partitioned(device, C.byref(d), int(part[0]), int(part[1]), C.byref(h))
+        else:
+            rc = L.cg_create(device, C.byref(d), mem_budget, C.byref(h))
         if rc != 0:
             raise CharonGpuError(f"cg_create failed ({rc}): {L.cg_last_error(None).decode()}")
         self._h = h
         self._model_keep = None
+
+    # ---- row-range partitioned filter -----------------------------------------------------------
+    def partition(self, rank, world):
+        """Keep only rows of part `rank` of `world` of a replicated filter (cg_partition_from_replicated)."""
+        self._check(self._L.cg_partition_from_replicated(self._h, rank, world), "cg_partition_from_replicated")
+
+    def export_partition(self) -> bytes:
+        buf = C.create_string_buffer(64)
+        self._check(self._L.cg_partition_export(self._h, buf), "cg_partition_export")
+        return buf.raw
+
+    def attach_ipc(self, peer_part: int, handle: bytes):
+        self._check(self._L.cg_partition_attach_ipc(self._h, peer_part, C.create_string_buffer(handle, 64)), "cg_partition_attach_ipc")
+
+    def attach_peer(self, peer_part: int, peer: "GpuClassifier"):
+        self._check(self._L.cg_partition_attach_peer(self._h, peer_part, peer._h), "cg_partition_attach_peer")
 
     # ---- plumbing -----------------------------------------------------------------------------------------
     def _check(self, rc, what):

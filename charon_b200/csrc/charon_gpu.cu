@@ -59,6 +59,11 @@ struct cg_handle {
     bool single_pass = false;
     void *d_filter = nullptr;
     size_t filter_bytes = 0;
+    // row-range partition (0 parts = replicated): this GPU stores rows [row_begin, row_begin + local_rows)
+    uint32_t n_parts = 0, my_part = 0, rows_per_part = 0;
+    uint64_t row_begin = 0, local_rows = 0;
+    const void *part_base[CG_MAX_PARTS] = {};
+    bool part_ipc[CG_MAX_PARTS] = {};
     uint8_t *d_bin_to_cat = nullptr;
     uint8_t h_bin_to_cat[256];
     // model
@@ -122,6 +127,8 @@ cgk::CountParams make_params(cg_handle *h) {
     P.seg_len = nullptr;
     P.long_read_min = 0; P.long_only = 0;
     P.dbg_out = nullptr; P.dbg_cap = 0; P.dbg_n = nullptr;
+    P.n_parts = h->n_parts; P.my_part = h->my_part; P.rows_per_part = h->rows_per_part; P.part_pad = 0;
+    for (int i = 0; i < CG_MAX_PARTS; ++i) P.part_base[i] = h->part_base[i];
     return P;
 }
 
@@ -185,6 +192,10 @@ template <int MODE> int occupancy_mode() {
 
 int launch_count(cg_handle *h, const cgk::CountParams &P) {
     if (P.n_reads == 0) return 0;
+    if (h->n_parts && P.filter) {
+        for (uint32_t p = 0; p < h->n_parts; ++p)
+            if (!h->part_base[p]) return fail(h, CG_ERR_STATE, "partitioned filter: part %u of %u is not attached (cg_partition_attach_*)", p, h->n_parts);
+    }
     int grid = int(std::min<uint64_t>(uint64_t(h->sm_count) * h->grid_per_sm, P.n_reads));
     CU(h, cudaMemsetAsync(h->counter.p, 0, 4, h->stream));
     cudaError_t e;

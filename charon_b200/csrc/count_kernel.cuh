@@ -18,6 +18,7 @@ namespace cgk {
 constexpr int NT = 128;          // threads per CTA
 constexpr int TK_CAP = 3072;     // k-mers per tile held in shared memory
 constexpr uint32_t INV5 = 0xCCCCCCCDu;  // 5^-1 mod 2^32 (exact division of multiples of 5)
+#define CG_MAX_PARTS 16
 
 struct CountParams {
     const uint8_t *bases;
@@ -47,6 +48,11 @@ struct CountParams {
     uint64_t *dbg_out;
     unsigned long long dbg_cap;
     unsigned long long *dbg_n;
+    // row-range partitioned filter: part p holds rows [p*rows_per_part, (p+1)*rows_per_part) in its own
+    // allocation on GPU p; remote parts are NVLink peer mappings.  n_parts == 0: `filter` is the whole (replicated) filter.
+    uint32_t n_parts, my_part;
+    uint32_t rows_per_part, part_pad;   // rows are < 2^32 (bin_size <= 2^32 - 3)
+    const void *part_base[CG_MAX_PARTS];
 };
 
 __constant__ uint64_t c_ibf_seeds[5] = {13572355802537770549ULL, 13043817825332782213ULL, 10650232656628343401ULL,
@@ -76,6 +82,29 @@ __device__ __forceinline__ uint4 ldg_stream_v4(const uint4 *p, uint64_t pol) {
     asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.u32 {%0, %1, %2, %3}, [%4], %5;"
                  : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p), "l"(pol));
     return v;
+}
+
+// remote (peer-mapped) rows: plain read-only loads, no local-L2 residency hint
+template <int MODE>
+__device__ __forceinline__ Mask<(MODE == 2 ? 2 : (MODE == 3 ? 4 : 1))> fetch_row_remote(const void *part, uint64_t row, uint32_t row_shift) {
+    Mask<(MODE == 2 ? 2 : (MODE == 3 ? 4 : 1))> m;
+    if (MODE == 0) {
+        const uint64_t bit = row << row_shift;
+        const uint32_t word = __ldg(reinterpret_cast<const uint32_t *>(part) + (bit >> 5));
+        const uint32_t rb = 1u << row_shift;
+        const uint32_t msk = rb >= 32 ? 0xFFFFFFFFu : ((1u << rb) - 1u);
+        m.w[0] = (word >> (uint32_t(bit) & 31u)) & msk;
+    } else if (MODE == 1) {
+        m.w[0] = __ldg(reinterpret_cast<const unsigned long long *>(part) + row);
+    } else if (MODE == 2) {
+        const ulonglong2 a = __ldg(reinterpret_cast<const ulonglong2 *>(part) + row);
+        m.w[0] = a.x; m.w[1] = a.y;
+    } else {
+        const ulonglong2 a = __ldg(reinterpret_cast<const ulonglong2 *>(part) + row * 2);
+        const ulonglong2 b = __ldg(reinterpret_cast<const ulonglong2 *>(part) + row * 2 + 1);
+        m.w[0] = a.x; m.w[1] = a.y; m.w[2] = b.x; m.w[3] = b.y;
+    }
+    return m;
 }
 
 // seqan3 interleaved_bloom_filter::hash_and_fit without the final * technical_bins
@@ -113,9 +142,37 @@ __device__ __forceinline__ Mask<ModeTraits<MODE>::NW> fetch_row(const void *filt
     return m;
 }
 
+// Partitioned filter: rows owned by other GPUs are read through their NVLink peer mappings.  Kept out of line so that
+// the replicated hot path keeps its register allocation.
+template <int MODE>
+__device__ __noinline__ Mask<ModeTraits<MODE>::NW> bulk_contains_partitioned(const CountParams &P, uint64_t value, uint64_t pol) {
+    constexpr int NW = ModeTraits<MODE>::NW;
+    Mask<NW> acc;
+#pragma unroll
+    for (int j = 0; j < NW; ++j) acc.w[j] = ~uint64_t(0);
+    Mask<NW> r[5];
+#pragma unroll
+    for (int i = 0; i < 5; ++i)
+        if (i < int(P.hash_funs)) {
+            const uint32_t row = uint32_t(ibf_row(value, c_ibf_seeds[i], P.hash_shift, P.bin_size));   // rows < 2^32
+            const uint32_t owner = row / P.rows_per_part;
+            const uint64_t local = row - owner * P.rows_per_part;
+            if (owner == P.my_part) r[i] = fetch_row<MODE>(P.filter, local, P.row_shift, pol);
+            else r[i] = fetch_row_remote<MODE>(P.part_base[owner], local, P.row_shift);
+        }
+#pragma unroll
+    for (int i = 0; i < 5; ++i)
+        if (i < int(P.hash_funs)) {
+#pragma unroll
+            for (int j = 0; j < NW; ++j) acc.w[j] &= r[i].w[j];
+        }
+    return acc;
+}
+
 template <int MODE>
 __device__ __forceinline__ Mask<ModeTraits<MODE>::NW> bulk_contains(const CountParams &P, uint64_t value, uint64_t pol) {
     constexpr int NW = ModeTraits<MODE>::NW;
+    if (P.n_parts) return bulk_contains_partitioned<MODE>(P, value, pol);
     Mask<NW> acc;
     uint64_t rows[5];
 #pragma unroll

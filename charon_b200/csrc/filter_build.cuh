@@ -71,6 +71,7 @@ struct SdDecodeParams {
     uint32_t technical_bins, bins, row_shift;
     void *filter;
     unsigned long long *errors;      // [0] position out of range, [1] bin >= bins
+    uint64_t row_begin, row_end;     // partitioned filter: only rows in [row_begin, row_end) are kept, stored relative to row_begin
 };
 
 __global__ void sd_decode_kernel(const SdDecodeParams P) {
@@ -92,9 +93,11 @@ __global__ void sd_decode_kernel(const SdDecodeParams P) {
             const uint64_t pos = ((q - j) << P.wl) | lo;
             ++j;
             if (pos >= P.size_bits) { atomicAdd(&P.errors[0], 1ull); continue; }
-            const uint64_t row = pos / P.technical_bins;
+            uint64_t row = pos / P.technical_bins;
             const uint32_t bin = uint32_t(pos % P.technical_bins);
             if (bin >= P.bins) { atomicAdd(&P.errors[1], 1ull); continue; }
+            if (row < P.row_begin || row >= P.row_end) continue;
+            row -= P.row_begin;
             if (rb <= 32) {
                 const uint64_t bit = (row << P.row_shift) + bin;
                 atomicOr(reinterpret_cast<uint32_t *>(P.filter) + (bit >> 5), 1u << (uint32_t(bit) & 31u));

@@ -69,7 +69,8 @@ public:
         d.sd_wl = idx_.sd_wl; d.ncat = ncat_; d.bin_to_cat = b2c.data();
         for (int g = 0; g < opt_.gpus; ++g) {
             std::unique_ptr<GpuSlice> s(new GpuSlice);
-            if (cg_create(g, &d, 0, &s->h) != 0) {
+            const bool part = opt_.partition_filter && opt_.gpus > 1;
+            if ((part ? cg_create_partitioned(g, &d, uint32_t(g), uint32_t(opt_.gpus), &s->h) : cg_create(g, &d, 0, &s->h)) != 0) {
                 const std::string m = cg_last_error(nullptr);
                 CH_ERROR(log_, "GPU %d: %s", g, m.c_str());
                 std::fprintf(stderr, "charon: GPU %d: %s\n", g, m.c_str());
@@ -77,6 +78,15 @@ public:
             }
             gpu_.push_back(std::move(s));
         }
+        if (opt_.partition_filter && opt_.gpus > 1)
+            for (int g = 0; g < opt_.gpus; ++g)
+                for (int q = 0; q < opt_.gpus; ++q)
+                    if (q != g && cg_partition_attach_peer(gpu_[size_t(g)]->h, uint32_t(q), gpu_[size_t(q)]->h) != 0) {
+                        const std::string m = cg_last_error(gpu_[size_t(g)]->h);
+                        CH_ERROR(log_, "GPU %d: %s", g, m.c_str());
+                        std::fprintf(stderr, "charon: GPU %d: %s\n", g, m.c_str());
+                        return 1;
+                    }
         std::vector<uint64_t>().swap(idx_.sd_low); std::vector<uint64_t>().swap(idx_.sd_high);   // the filter now lives in HBM
         model_ = StatsModel(opt_, ncat_);
         if (opt_.run_extract) cache_capacity_ = size_t(opt_.num_reads_to_fit) * ncat_ * 4;   // result.hpp:84 (reserve == capacity)

@@ -48,6 +48,7 @@ struct Options {
     // B200 extensions (not in the reference CLI)
     int gpus = 1;
     uint32_t batch_reads = 16384;
+    bool partition_filter = false;   // split the filter by row range over --gpus GPUs instead of replicating it
 
     static Options dehost_defaults() { return Options(); }
     static Options classify_defaults() {   // classify_arguments.hpp:16-39

@@ -148,6 +148,22 @@ int cg_create(int device, const cg_index_desc *desc, size_t mem_budget_bytes, cg
  * InputStats::hashes_per_bin (include/input_stats.hpp:19).  The handle is then ready for classification; the filter
  * can be exported with cg_debug_dump_filter to write an .idx file. */
 int cg_build_index(int device, const cg_build_desc *desc, size_t mem_budget_bytes, uint64_t *hashes_per_bin, cg_handle **out);
+/* ---- filter partitioned by row (bit-address) range across GPUs (BASELINE config 4) ----------------
+ * For an index whose filter must not be replicated (memory budget), GPU `part_rank` of `part_world` stores rows
+ * [part_rank * rpp, (part_rank + 1) * rpp) only (rpp = ceil(bin_size / part_world) rounded up to 64).  Reads stay
+ * sharded across GPUs; the count kernel fetches rows owned by other GPUs through NVLink/NVSwitch peer mappings of
+ * their partitions, so bulk_contains (include/index.hpp:110-112) keeps its exact AND-of-rows semantics and
+ * unique_counts (read_entry.hpp:122-136) need no per-minimiser exchange.  All parts must be attached before the
+ * first batch.  Exchange of the 64-byte handles between processes is the caller's job (torch.distributed, MPI, ...). */
+int cg_create_partitioned(int device, const cg_index_desc *desc, uint32_t part_rank, uint32_t part_world, cg_handle **out);
+/* Turn a replicated handle (cg_create / cg_build_index) into part `part_rank` of `part_world`: frees the other rows. */
+int cg_partition_from_replicated(cg_handle *h, uint32_t part_rank, uint32_t part_world);
+/* cudaIpcMemHandle_t (64 bytes) of this GPU's partition, for a peer PROCESS. */
+int cg_partition_export(cg_handle *h, void *ipc_handle_64);
+int cg_partition_attach_ipc(cg_handle *h, uint32_t peer_part, const void *ipc_handle_64);
+/* Peer handle living in the SAME process (one host thread per GPU): enables peer access and uses its pointer. */
+int cg_partition_attach_peer(cg_handle *h, uint32_t peer_part, cg_handle *peer);
+
 void cg_destroy(cg_handle *h);
 const char *cg_last_error(const cg_handle *h);
 /* Use an externally created cudaStream_t (e.g. torch's current stream) for all work; NULL = own stream. */

@@ -273,3 +273,26 @@ def test_classify_three_categories(charon, tmp_path):
             assert wp[4] == gp[4] or abs(float(wp[4]) - float(gp[4])) <= 1e-4 * max(abs(float(wp[4])), 1e-30)
     same_call = sum(w.split("\t")[:3] == g.split("\t")[:3] for w, g in zip(wl, gl))
     assert same_call >= len(wl) - 2
+
+
+def _n_gpus():
+    try:
+        import torch
+        return torch.cuda.device_count()
+    except Exception:
+        return 0
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("extra", [[], ["--partition_filter"]])
+def test_dehost_two_gpus_same_bytes(charon, small_index, tmp_path, extra):
+    if _n_gpus() < 2:
+        pytest.skip("needs two GPUs")
+    idx, refs, idx_path = small_index
+    reads = _mixed_reads(refs, 500, seed=15)
+    fq = str(tmp_path / "r.fq")
+    _write_fastq(fq, reads)
+    want = _oracle_tsv(idx, [(r,) for r in reads], oracle.default_options(True))
+    got = run(charon, "dehost", fq, "--db", idx_path, "--gpus", "2", "--batch_reads", "60", *extra, cwd=tmp_path)
+    assert got.returncode == 0, got.stderr
+    assert got.stdout == want
