@@ -149,7 +149,7 @@ def run_reference(args, wl):
                              "sample": f"{n} reads/step x {args.steps} steps; hot path only; with gzip ratio: {cb['with_gzip_value']:.1f} reads/s"},
             "gbases_per_sec": val * wl["read_len"] / 1e9,
             "e2e": {"value": val, "unit": "reads/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def run_b200(args, wl):
@@ -287,13 +287,30 @@ def run_b200(args, wl):
                                       np.array_equal(g["unique_counts"], sr["unique_counts"]) and np.array_equal(g["call"], sr["call"]) and
                                       np.array_equal(g["confidence"], sr["confidence"]))
         line["cpu_baseline"] = cb
-    print(json.dumps(line), flush=True)
+    emit(line)
     gpu.close()
     if dist is not None:
         dist.destroy_process_group()
 
 
+_REAL_STDOUT = None
+
+
+def emit(line: dict):
+    """The ONE JSON line goes to the process's original stdout; everything else (NCCL banners, library chatter) was
+    re-routed to stderr in main()."""
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
+
+
 def main():
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=8)
@@ -314,6 +331,7 @@ def main():
         # launched without torchrun: re-exec under torch.distributed.run
         cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}", "--master-addr", "127.0.0.1",
                "--master-port", "29511"] + sys.argv
+        os.dup2(_REAL_STDOUT, 1)   # the child sets up its own re-routing
         os.execv(sys.executable, cmd)
     run_b200(args, wl)
 
