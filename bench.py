@@ -224,17 +224,44 @@ def run_b200(args, wl):
     res = gpu.fetch_staged(True)
     minimisers = int(res["num_hashes"].astype(np.int64).sum())
     total_ms_max = max_over_ranks(total_ms)
-    # ---- end-to-end arm: host buffers through the C-ABI call ----------------------------------------------------
-    for _ in range(max(1, min(args.warmup, 2))):
-        gpu._check(Lb.cg_classify_batch(gpu._h, C.byref(batch), C.byref(sc), C.byref(co), C.byref(ca)), "cg_classify_batch")
+    # ---- end-to-end arm: host buffers through the C-ABI (H2D + kernels + D2H of every step inside the timed region) -------
+    # cg_submit_batch / cg_wait_batch on two slots: the PCIe copy of step i+1 overlaps the kernels of step i
+    out2 = dict(num_hashes=pinned_array((R,), np.uint32), counts=pinned_array((R, 2), np.uint32), unique_counts=pinned_array((R, 2), np.uint32),
+                prob=pinned_array((R, 2), np.float64), call=pinned_array((R,), np.uint8), confidence=pinned_array((R,), np.uint8))
+    co2 = A.CountsOut(out2["num_hashes"].ctypes.data, out2["counts"].ctypes.data, out2["unique_counts"].ctypes.data)
+    ca2 = A.CallsOut(out2["prob"].ctypes.data, out2["call"].ctypes.data, out2["confidence"].ctypes.data)
+    slots = [(co, ca), (co2, ca2)]
+
+    def e2e_steps(n):
+        for i in range(n):
+            sl = i & 1
+            if i >= 2:
+                gpu._check(Lb.cg_wait_batch(gpu._h, sl), "cg_wait_batch")
+            gpu._check(Lb.cg_submit_batch(gpu._h, sl, C.byref(batch), C.byref(sc), C.byref(slots[sl][0]), C.byref(slots[sl][1])), "cg_submit_batch")
+        gpu._check(Lb.cg_wait_batch(gpu._h, 0), "cg_wait_batch")
+        gpu._check(Lb.cg_wait_batch(gpu._h, 1), "cg_wait_batch")
+
+    e2e_steps(max(2, min(args.warmup, 3)))
     barrier()
     gpu.timer_start()
-    for _ in range(args.steps):
-        gpu._check(Lb.cg_classify_batch(gpu._h, C.byref(batch), C.byref(sc), C.byref(co), C.byref(ca)), "cg_classify_batch")
+    e2e_steps(args.steps)
     e2e_ms, _, _, _ = gpu.timer_stop()
     barrier()
     e2e_ms_max = max_over_ranks(e2e_ms)
     assert np.array_equal(out["num_hashes"], res["num_hashes"]) and np.array_equal(out["call"], res["call"])
+    assert args.steps < 2 or (np.array_equal(out2["num_hashes"], res["num_hashes"]) and np.array_equal(out2["call"], res["call"]))
+    # ---- serial variant of the same call (cg_classify_batch: copy, kernels, copy back, one after the other) -----------------
+    gpu._check(Lb.cg_classify_batch(gpu._h, C.byref(batch), C.byref(sc), C.byref(co), C.byref(ca)), "cg_classify_batch")
+    barrier()
+    gpu.timer_start()
+    for _ in range(args.steps):
+        gpu._check(Lb.cg_classify_batch(gpu._h, C.byref(batch), C.byref(sc), C.byref(co), C.byref(ca)), "cg_classify_batch")
+    serial_ms, _, _, _ = gpu.timer_stop()
+    barrier()
+    serial_ms_max = max_over_ranks(serial_ms)
+    # ---- what the memory system gives a kernel that ONLY gathers, on this very filter -------------------------
+    g_query_ms = gpu.bench_gather(minimisers, mode=0, reps=5)
+    g_sector_ms = gpu.bench_gather(3 * minimisers, mode=1, reps=5)
     info = gpu.info()
     if rank != 0:
         return
@@ -268,14 +295,22 @@ def run_b200(args, wl):
                        "index_build_on_gpu_s": round(build_s, 2)},
             "gbases_per_sec": value * L / 1e9,
             "e2e": {"value": e2e, "unit": "reads/s", "h2d_bytes_per_step": int(R * L + (R + 1) * 8 + R * 12) * world,
-                    "d2h_bytes_per_step": int(R * (4 + 8 + 8 + 16 + 2)) * world, "gbases_per_sec": e2e * L / 1e9},
+                    "d2h_bytes_per_step": int(R * (4 + 8 + 8 + 16 + 2)) * world, "gbases_per_sec": e2e * L / 1e9,
+                    "api": "cg_submit_batch/cg_wait_batch, two slots (copy of step i+1 overlaps kernels of step i)",
+                    "serial_cg_classify_batch_value": reads_total / (serial_ms_max / 1e3)},
             "gpu_launches": int(3 * args.steps),
             "clocks": clocks,
             "roofline": {"bound": "hbm", "kernel": "cgk::count_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": traffic,
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs (burst copy)" if peaks else "fallback 6650",
                          "algorithmic_bytes_per_launch": algo_bytes, "avg_launch_ms": avg_count_ms,
-                         "count_kernel_share_of_step": count_ms / total_ms, "eval_kernels_ms_per_step": eval_ms / max(n_runs, 1),
+                         "count_kernel_share_of_step": count_ms / total_ms,
+                         "gather_microbench": {
+                             "what": "same filter, same 3-row addressing, nothing else in the kernel (cg_bench_gather mode 0) / one random 32 B sector per load (mode 1)",
+                             "query_addressing_GBps": ALGO_BYTES_PER_MINIMISER * minimisers / (g_query_ms / 1e3) / 1e9,
+                             "pure_sector_GBps": 32 * 3 * minimisers / (g_sector_ms / 1e3) / 1e9,
+                             "count_kernel_gather_GBps": ALGO_BYTES_PER_MINIMISER * minimisers / (avg_count_ms / 1e3) / 1e9,
+                             "frac_of_achievable_gather": (g_query_ms / avg_count_ms)}, "eval_kernels_ms_per_step": eval_ms / max(n_runs, 1),
                          "note": "96 B/minimiser + 1 B/base (SURVEY 8d) regardless of L2 hits; compacted filter of this workload is "
                                  f"{info.filter_bytes / 1e6:.0f} MB"}}
     if world == 1 and not args.no_cpu_baseline:

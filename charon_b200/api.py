@@ -62,7 +62,7 @@ class Info(C.Structure):
 EXPORTS = ["cg_create", "cg_build_index", "cg_destroy", "cg_last_error", "cg_set_stream", "cg_sync", "cg_set_model", "cg_count_batch", "cg_eval_batch",
            "cg_classify_batch", "cg_stage_batch", "cg_run_staged", "cg_fetch_staged", "cg_get_info", "cg_host_alloc", "cg_host_free", "cg_timer_start", "cg_timer_stop", "cg_debug_minimisers",
            "cg_debug_query", "cg_debug_dump_filter", "cg_debug_force_generic", "cg_create_partitioned", "cg_partition_from_replicated",
-           "cg_partition_export", "cg_partition_attach_ipc", "cg_partition_attach_peer"]
+           "cg_partition_export", "cg_partition_attach_ipc", "cg_partition_attach_peer", "cg_bench_gather", "cg_submit_batch", "cg_wait_batch"]
 
 _lib = None
 
@@ -84,6 +84,9 @@ def load_library():
     L.cg_partition_export.argtypes = [vp, vp]
     L.cg_partition_attach_ipc.argtypes = [vp, u32, vp]
     L.cg_partition_attach_peer.argtypes = [vp, u32, vp]
+    L.cg_submit_batch.argtypes = [vp, i32, P(Batch), P(ReadScalars), P(CountsOut), P(CallsOut)]
+    L.cg_wait_batch.argtypes = [vp, i32]
+    L.cg_bench_gather.argtypes = [vp, u64, i32, i32, P(f32)]
     L.cg_destroy.argtypes = [vp]; L.cg_destroy.restype = None
     L.cg_last_error.argtypes = [vp]; L.cg_last_error.restype = C.c_char_p
     L.cg_set_stream.argtypes = [vp, vp]
@@ -331,6 +334,24 @@ class GpuClassifier:
         self._check(self._L.cg_classify_batch(self._h, C.byref(b), C.byref(sc), C.byref(co), C.byref(ca)), "cg_classify_batch")
         return res
 
+    # two-slot pipeline ------------------------------------------------------------------------------------------
+    def submit(self, slot, bases, seg_off, mean_q=None, compression=None, length=None, read_seg=None):
+        """cg_submit_batch: returns at once; the result dict is filled when wait(slot) returns."""
+        b, keep, n = self._batch(bases, seg_off, read_seg)
+        with_calls = mean_q is not None
+        sc, keep2 = self._scalars(n, mean_q, compression, length) if with_calls else (None, None)
+        res, co, ca = self._outs(n, with_calls)
+        self._check(self._L.cg_submit_batch(self._h, slot, C.byref(b), C.byref(sc) if with_calls else None, C.byref(co),
+                                            C.byref(ca) if with_calls else None), "cg_submit_batch")
+        if not hasattr(self, "_inflight"):
+            self._inflight = {}
+        self._inflight[slot] = (b, keep, sc, keep2, co, ca, res)   # host buffers must outlive the wait
+        return res
+
+    def wait(self, slot):
+        self._check(self._L.cg_wait_batch(self._h, slot), "cg_wait_batch")
+        return self._inflight.pop(slot)[-1] if getattr(self, "_inflight", {}).get(slot) else None
+
     def eval_batch(self, num_hashes, counts, unique_counts, mean_q, compression, length):
         n = len(num_hashes)
         nh = np.ascontiguousarray(num_hashes, np.uint32); ct = np.ascontiguousarray(counts, np.uint32); uq = np.ascontiguousarray(unique_counts, np.uint32)
@@ -357,6 +378,12 @@ class GpuClassifier:
         res, co, ca = self._outs(self._staged_n, with_calls)
         self._check(self._L.cg_fetch_staged(self._h, C.byref(co), C.byref(ca) if ca is not None else None), "cg_fetch_staged")
         return res
+
+    def bench_gather(self, n_values, mode=0, reps=5) -> float:
+        """Average ms of the random-gather microbenchmark (cg_bench_gather) on this filter."""
+        ms = f32(0)
+        self._check(self._L.cg_bench_gather(self._h, int(n_values), mode, reps, C.byref(ms)), "cg_bench_gather")
+        return float(ms.value)
 
     def timer_start(self):
         self._check(self._L.cg_timer_start(self._h), "cg_timer_start")

@@ -9,6 +9,7 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <utility>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
@@ -21,6 +22,7 @@
 #include "count_kernel_v3.cuh"
 #include "eval_kernel.cuh"
 #include "filter_build.cuh"
+#include "gather_bench.cuh"
 
 namespace {
 
@@ -83,6 +85,36 @@ struct cg_handle {
     uint64_t staged_max_read_len = 0;
     bool force_cta = false;       // test hook: CTA-per-read kernel for every read
     bool force_generic = false;   // test hook: run the any-(k,w) kernel even when the specialised one applies
+    // second pipeline slot (cg_submit_batch / cg_wait_batch): the fields above always describe the ACTIVE slot; the other
+    // slot's stream, events and batch buffers are parked here and swapped in when that slot is addressed.
+    struct Parked {
+        cudaStream_t stream = nullptr;
+        cudaEvent_t ev[8] = {};
+        DevBuf bases, seg_off, read_seg, num_hashes, counts, unique, prob, call, conf, mq, cr, len, counter;
+        uint32_t staged_reads = 0, staged_segs = 0;
+        uint64_t staged_bases = 0, staged_max_read_len = 0;
+        bool staged_has_read_seg = false, staged_has_scalars = false;
+        bool created = false, pending = false;
+        cg_counts_out co{}; cg_calls_out ca{}; bool has_co = false, has_ca = false;
+    } parked;
+    int active_slot = 0;
+    bool active_pending = false;
+    cg_counts_out act_co{}; cg_calls_out act_ca{}; bool act_has_co = false, act_has_ca = false;
+    cudaEvent_t join_ev = nullptr;
+    void swap_slots() {
+        std::swap(stream, parked.stream);
+        for (int i = 0; i < 8; ++i) std::swap(ev[i], parked.ev[i]);
+        std::swap(bases, parked.bases); std::swap(seg_off, parked.seg_off); std::swap(read_seg, parked.read_seg);
+        std::swap(num_hashes, parked.num_hashes); std::swap(counts, parked.counts); std::swap(unique, parked.unique);
+        std::swap(prob, parked.prob); std::swap(call, parked.call); std::swap(conf, parked.conf);
+        std::swap(mq, parked.mq); std::swap(cr, parked.cr); std::swap(len, parked.len); std::swap(counter, parked.counter);
+        std::swap(staged_reads, parked.staged_reads); std::swap(staged_segs, parked.staged_segs);
+        std::swap(staged_bases, parked.staged_bases); std::swap(staged_max_read_len, parked.staged_max_read_len);
+        std::swap(staged_has_read_seg, parked.staged_has_read_seg); std::swap(staged_has_scalars, parked.staged_has_scalars);
+        std::swap(active_pending, parked.pending);
+        std::swap(act_co, parked.co); std::swap(act_ca, parked.ca); std::swap(act_has_co, parked.has_co); std::swap(act_has_ca, parked.has_ca);
+        active_slot ^= 1;
+    }
     // stats
     cg_info info{};
     // cg_timer_*: one outer event pair + three events per run recorded while timing
@@ -295,6 +327,7 @@ int validate_batch(cg_handle *h, const cg_batch *b) {
 
 // H2D of one batch (src/dehost_main.cpp:335-339: the chunk of records handed to the loop)
 int stage(cg_handle *h, const cg_batch *b, const cg_read_scalars *sc) {
+    if (h->active_pending) return fail(h, CG_ERR_STATE, "a submitted batch is still in flight on this slot: cg_wait_batch first");
     int rc = validate_batch(h, b);
     if (rc) return rc;
     const uint64_t nbases = b->n_segs ? b->seg_off[b->n_segs] : 0;
@@ -345,7 +378,7 @@ int run(cg_handle *h, bool with_eval) {
     return 0;
 }
 
-int fetch(cg_handle *h, const cg_counts_out *co, const cg_calls_out *ca) {
+int fetch_enqueue(cg_handle *h, const cg_counts_out *co, const cg_calls_out *ca) {
     const size_t n = h->staged_reads, nc = h->ncat;
     CU(h, cudaEventRecord(h->ev[5], h->stream));
     if (n) {
@@ -361,6 +394,9 @@ int fetch(cg_handle *h, const cg_counts_out *co, const cg_calls_out *ca) {
         }
     }
     CU(h, cudaEventRecord(h->ev[6], h->stream));
+    return 0;
+}
+int fetch_finish(cg_handle *h) {
     CU(h, cudaStreamSynchronize(h->stream));
     float ms = 0;
     if (cudaEventElapsedTime(&ms, h->ev[0], h->ev[1]) == cudaSuccess) h->info.last_h2d_ms = ms;
@@ -369,6 +405,10 @@ int fetch(cg_handle *h, const cg_counts_out *co, const cg_calls_out *ca) {
     if (cudaEventElapsedTime(&ms, h->ev[5], h->ev[6]) == cudaSuccess) h->info.last_d2h_ms = ms;
     cudaGetLastError();
     return 0;
+}
+int fetch(cg_handle *h, const cg_counts_out *co, const cg_calls_out *ca) {
+    int rc = fetch_enqueue(h, co, ca);
+    return rc ? rc : fetch_finish(h);
 }
 
 }  // namespace

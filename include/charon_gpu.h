@@ -184,6 +184,15 @@ int cg_eval_batch(cg_handle *h, uint32_t n_reads, const uint32_t *num_hashes, co
 int cg_classify_batch(cg_handle *h, const cg_batch *batch, const cg_read_scalars *scalars,
                       const cg_counts_out *counts_out, const cg_calls_out *calls_out);
 
+/* ---- two-slot pipeline over the same path: cg_submit_batch enqueues H2D + kernels + D2H of one batch on the slot's
+ * own stream and returns; cg_wait_batch blocks until that slot's outputs are in the caller's buffers.  With slots 0/1
+ * used alternately the PCIe copy of batch i+1 overlaps the kernels of batch i (the chunk loop of
+ * src/dehost_main.cpp:335-381 software-pipelined).  Host buffers must stay valid (and should be pinned) until the wait.
+ * scalars == NULL: counts only (no model evaluation). */
+int cg_submit_batch(cg_handle *h, int slot, const cg_batch *batch, const cg_read_scalars *scalars,
+                    const cg_counts_out *counts_out, const cg_calls_out *calls_out);
+int cg_wait_batch(cg_handle *h, int slot);
+
 /* ---- staged (device-resident) variant used to time the kernels without PCIe -------------- */
 int cg_stage_batch(cg_handle *h, const cg_batch *batch, const cg_read_scalars *scalars);  /* H2D only */
 int cg_run_staged(cg_handle *h, int with_eval);                                            /* kernels only, async */
@@ -196,6 +205,11 @@ void cg_host_free(void *p);
  * cg_run_staged / cg_classify_batch in between records per-launch events so the count kernel's own duration is known. */
 int cg_timer_start(cg_handle *h);
 int cg_timer_stop(cg_handle *h, float *total_ms, float *count_kernel_ms_sum, float *eval_kernel_ms_sum, uint32_t *n_runs);
+
+/* SURVEY 8(d) denominator: random 32-byte-sector gather rate on this handle's filter, measured with nothing else in the
+ * kernel.  mode 0: the query's own addressing (hash_funs rows per value, i.e. 96 B algorithmic per value for 3 hashes);
+ * mode 1: one random 32-bit load per value (32 B sector each).  avg_ms = mean of `reps` launches after a warm-up. */
+int cg_bench_gather(cg_handle *h, uint64_t n_values, int mode, int reps, float *avg_ms);
 
 /* ---- introspection ----------------------------------------------------------------------- */
 typedef struct cg_info {

@@ -268,3 +268,33 @@ def test_tie_run_crossing_a_tile_boundary_regression(small):
                 assert np.array_equal(gpu.debug_minimisers(s), np.sort(oracle.minimisers(s))), (mode, pad)
         finally:
             gpu.force_generic(0)
+
+
+@pytest.mark.gpu
+def test_two_slot_pipeline_matches_the_oracle():
+    """cg_submit_batch / cg_wait_batch: two different batches in flight at once, then reuse of both slots."""
+    import charon_b200
+    idx, refs = common.build_oracle_index([150_000, 110_000], [0, 1], ["host", "microbial"], seed=61)
+    gpu = common.gpu_from_oracle(idx)
+    gpu.set_model(charon_b200.DehostOptions(), host_index=idx.host_index)
+    batches = []
+    for i, (n, L) in enumerate([(300, 3000), (150, 5000), (64, 700), (500, 1500)]):
+        bases, seg_off, _ = common.fixed_length_batch(70 + i, refs, [0.45, 0.45], n, L)
+        mq, cr = common.scalars(n, np.random.default_rng(i))
+        batches.append((bases, seg_off, mq, cr, np.full(n, L, np.uint32)))
+    want = [idx.classify_batch(b, s, mean_q=mq, compression=cr) for b, s, mq, cr, _ in batches]
+    r0 = gpu.submit(0, *batches[0])
+    r1 = gpu.submit(1, *batches[1])
+    with pytest.raises(charon_b200.CharonGpuError, match="in flight"):
+        gpu.submit(1, *batches[2])
+    gpu.wait(0)
+    r2 = gpu.submit(0, *batches[2])
+    gpu.wait(1)
+    r3 = gpu.submit(1, batches[3][0], batches[3][1])        # counts only on the second use of slot 1
+    gpu.wait(0); gpu.wait(1)
+    for got, w in zip((r0, r1, r2), want[:3]):
+        common.assert_parity(got, w)
+    common.assert_parity(r3, want[3])
+    # the synchronous call still works afterwards
+    common.assert_parity(gpu.classify_batch(*batches[0]), want[0])
+    gpu.close()
