@@ -3,7 +3,7 @@
 // Same arithmetic, same exactness argument, but the unit of work is a WARP: each warp owns one read at a time and walks
 // it in tiles of 31*23 = 713 windows, so there is no CTA-wide barrier anywhere on the hot path (only __syncwarp).  Warps
 // drift apart in phase, which lets one warp's load / gather latency hide behind the others' arithmetic, and the next
-// tile's bases are prefetched into registers (tagged by address) while the current tile is processed.
+// tile's bases are prefetched with cp.async into a per-warp staging buffer (tagged by address) while the current tile is processed.
 // Reads longer than P.long_read_min are left to the CTA-per-read kernel (count_kernel_v2), launched afterwards on the
 // same stream, so that one very long read cannot serialise on a single warp.
 #pragma once
@@ -11,7 +11,13 @@
 
 namespace cgk {
 
-constexpr int WARPS3 = 4;              // warps per CTA (independent of each other)
+#ifndef CG_V3_WARPS
+#define CG_V3_WARPS 4
+#endif
+#ifndef CG_V3_MINB
+#define CG_V3_MINB 3
+#endif
+constexpr int WARPS3 = CG_V3_WARPS;    // warps per CTA (independent of each other)
 constexpr int WLIST_CAP = 256;         // compacted emission list of a warp tile (expected ~65 entries)
 
 template <int KK, int WW, bool SMALL> struct V3Cfg {
@@ -22,13 +28,14 @@ template <int KK, int WW, bool SMALL> struct V3Cfg {
     static constexpr int NVL = (NVEC + 31) / 32;          // vectors per lane
     static constexpr int NCNT = SMALL ? 8 : 256;
     static constexpr int CODES = ((32 + 16 * NVL * 32 + 64) + 15) / 16 * 16;
+    static constexpr int RAW = NVL * 32 * 16;     // cp.async staging of the next tile's ASCII bases
     static constexpr size_t WARP_BYTES = size_t(NK) * 8 + size_t(32) * PRIV_CAP * 8 + size_t(WLIST_CAP) * 8 + size_t(NCNT) * 8 + 32 +
-                                         size_t(NCNT) * 4 * 2 + CODES;
+                                         size_t(NCNT) * 4 * 2 + CODES + RAW;
     static constexpr size_t SMEM = 512 + WARPS3 * WARP_BYTES;
 };
 
 template <int MODE, int KK, int WW, bool SMALL>
-__global__ void __launch_bounds__(WARPS3 * 32, 4) count_kernel_v3(const CountParams P) {
+__global__ void __launch_bounds__(WARPS3 * 32, CG_V3_MINB) count_kernel_v3(const CountParams P) {
     using C2 = V2Cfg<KK, WW>;
     using C = V3Cfg<KK, WW, SMALL>;
     constexpr int NW = ModeTraits<MODE>::NW;
@@ -49,6 +56,7 @@ __global__ void __launch_bounds__(WARPS3 * 32, 4) count_kernel_v3(const CountPar
         S.uniq = S.cnt + C::NCNT;
         S.codes = reinterpret_cast<uint8_t *>(S.uniq + C::NCNT);
     }
+    uint4 *const raw = reinterpret_cast<uint4 *>(S.codes + C::CODES);   // 16-byte aligned: every term of WARP_BYTES is a multiple of 16
     __shared__ uint32_t s_nhash_w[WARPS3], s_carry_valid_w[WARPS3];
     __shared__ long long s_carry_pos_w[WARPS3];
     uint32_t *const s_nhash = &s_nhash_w[warp];
@@ -67,8 +75,8 @@ __global__ void __launch_bounds__(WARPS3 * 32, 4) count_kernel_v3(const CountPar
         return __shfl_sync(0xFFFFFFFFu, t, 0);
     };
     // prefetched vectors of the next tile, tagged by their (16-byte aligned) global address
-    uint4 pf[C::NVL];
     const uint8_t *pf_addr = nullptr;
+    const uint32_t raw_s = uint32_t(__cvta_generic_to_shared(raw));
     auto prefetch = [&](const uint8_t *gsrc, uint32_t nb) {
         const uint32_t head = uint32_t(reinterpret_cast<uintptr_t>(gsrc) & 15u);
         const uint4 *vsrc = reinterpret_cast<const uint4 *>(gsrc - head);
@@ -76,8 +84,10 @@ __global__ void __launch_bounds__(WARPS3 * 32, 4) count_kernel_v3(const CountPar
 #pragma unroll
         for (int q = 0; q < C::NVL; ++q) {
             const uint32_t i = lane + q * 32;
-            if (i < nvec) pf[q] = ldg_stream_v4(vsrc + i, pol_stream);
+            if (i < nvec)
+                asm volatile("cp.async.cg.shared.global.L2::cache_hint [%0], [%1], 16, %2;" ::"r"(raw_s + 16u * i), "l"(vsrc + i), "l"(pol_stream) : "memory");
         }
+        asm volatile("cp.async.commit_group;" ::: "memory");
         pf_addr = gsrc;
     };
 
@@ -123,6 +133,7 @@ __global__ void __launch_bounds__(WARPS3 * 32, 4) count_kernel_v3(const CountPar
             for (int j = 0; j < NW; ++j) bm[j] = S.bestmask[j];
             const bool last_pass = (pass == npass - 1);
 
+            uint32_t pend = 0;   // emitted values waiting at the front of S.list for a full group of 32 (warp-uniform)
             for (uint32_t seg = seg0; seg < seg1; ++seg) {
                 const uint64_t sbase = P.seg_off[seg];
                 const uint64_t slen = P.seg_len ? P.seg_len[seg] : P.seg_off[seg + 1] - sbase;
@@ -155,17 +166,20 @@ __global__ void __launch_bounds__(WARPS3 * 32, 4) count_kernel_v3(const CountPar
                     const uint32_t head = uint32_t(reinterpret_cast<uintptr_t>(gsrc) & 15u);
                     const uint32_t nvec = (head + nb + 15u) >> 4;
                     if (pf_addr != gsrc) prefetch(gsrc, nb);          // not predicted: load now
-                    __syncwarp();                                      // previous tile's readers of codes are done
+                    asm volatile("cp.async.wait_all;" ::: "memory");
+                    __syncwarp();                                      // staging complete for every lane; previous tile's readers of codes are done
 #pragma unroll
                     for (int q = 0; q < C::NVL; ++q) {
                         const uint32_t i = lane + q * 32;
                         if (i < nvec) {
+                            const uint4 x = raw[i];
                             uint4 y;
-                            y.x = encode4(S.lut, pf[q].x); y.y = encode4(S.lut, pf[q].y);
-                            y.z = encode4(S.lut, pf[q].z); y.w = encode4(S.lut, pf[q].w);
+                            y.x = encode4(S.lut, x.x); y.y = encode4(S.lut, x.y);
+                            y.z = encode4(S.lut, x.z); y.w = encode4(S.lut, x.w);
                             *reinterpret_cast<uint4 *>(S.codes + 32 + 16 * i) = y;
                         }
                     }
+                    __syncwarp();   // every lane has consumed its staged vectors: the buffer may be refilled
                     // predict + prefetch the next tile: next tile of this segment, else the next read's first tile
                     if (!last_tile) {
                         const uint64_t g1 = g0 + Tw - 1;
@@ -209,9 +223,11 @@ __global__ void __launch_bounds__(WARPS3 * 32, 4) count_kernel_v3(const CountPar
                             const uint64_t f = (uint64_t(Hi) * C2::P_KL + Lo) ^ seed, rc = (uint64_t(RHi) * C2::P_KL + RLo) ^ seed;
                             v[j] = umin64(f, rc);
                         }
-                        if (!full) {
+                        if (nk < uint32_t(C::NK)) {   // warp-uniform: only the last tile of a segment has k-mers past its end
+                            if (!full) {
 #pragma unroll
-                            for (int j = 0; j < WW; ++j) if (k0 + j >= nk) v[j] = VMAX;
+                                for (int j = 0; j < WW; ++j) if (k0 + j >= nk) v[j] = VMAX;
+                            }
                         }
                         uint64_t pm = v[0];
                         S.arr[k0] = pm;
@@ -249,9 +265,9 @@ __global__ void __launch_bounds__(WARPS3 * 32, 4) count_kernel_v3(const CountPar
 #pragma unroll
                     for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, inc, o); if (lane >= uint32_t(o)) inc += t; }
                     uint32_t nl = __shfl_sync(0xFFFFFFFFu, inc, 31);
-                    const bool redo = __any_sync(0xFFFFFFFFu, tie) || nl > WLIST_CAP;
+                    const bool redo = __any_sync(0xFFFFFFFFu, tie) || pend + nl > WLIST_CAP;
                     if (!redo) {
-                        uint32_t dst = inc - cnt;
+                        uint32_t dst = pend + inc - cnt;
                         for (uint32_t q = 0; q < cnt; ++q, ++dst) S.list[dst] = pslot0[q];
                         if (lane == 0) *s_carry_valid = 0;
                     } else {
@@ -274,19 +290,38 @@ __global__ void __launch_bounds__(WARPS3 * 32, 4) count_kernel_v3(const CountPar
                         unsigned long long base = 0;
                         if (lane == 0) base = atomicAdd(P.dbg_n, (unsigned long long)nl);
                         base = __shfl_sync(0xFFFFFFFFu, base, 0);
-                        for (uint32_t i = lane; i < nl; i += 32) if (base + i < P.dbg_cap) P.dbg_out[base + i] = S.list[i];
+                        for (uint32_t i = lane; i < nl; i += 32) if (base + i < P.dbg_cap) P.dbg_out[base + i] = S.list[pend + i];
                     }
-                    if (P.filter)
-                        for (uint32_t i = lane; i < nl; i += 32) {
+                    if (lane == 0 && do_tot && nl) atomicAdd(s_nhash, nl);
+                    if (P.filter) {
+                        // only full groups of 32 are queried now; the remainder waits for the next tile's emissions
+                        const uint32_t have = pend + nl, fullg = have & ~31u;
+                        for (uint32_t i = lane; i < fullg; i += 32) {
                             const Mask<NW> m = bulk_contains<MODE>(P, S.list[i], pol_filter);
                             T.add(m, bm, small_bins, do_tot, do_unq, S);
                         }
-                    if (lane == 0 && do_tot && nl) atomicAdd(s_nhash, nl);
+                        const uint32_t rem = have - fullg;
+                        if (fullg) {
+                            uint64_t x = 0;
+                            if (lane < rem) x = S.list[fullg + lane];
+                            __syncwarp();
+                            if (lane < rem) S.list[lane] = x;
+                        }
+                        pend = rem;
+                    }
                     if (last_tile) break;
                     g0 += Tw - 1;
                     first = false;
                 }  // tiles
             }      // segments
+            if (pend) {   // flush the last partial group of this pass
+                __syncwarp();
+                if (lane < pend) {
+                    const Mask<NW> m = bulk_contains<MODE>(P, S.list[lane], pol_filter);
+                    T.add(m, bm, small_bins, do_tot, do_unq, S);
+                }
+                pend = 0;
+            }
 
             if (small_bins) {
 #pragma unroll
