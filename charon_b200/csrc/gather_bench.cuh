@@ -33,7 +33,17 @@ __global__ void __launch_bounds__(256) gather_bench_kernel(const CountParams P, 
             if (mode == 0) m[u] = bulk_contains<MODE>(P, v, pol);
             else {
                 const uint64_t w = __umul64hi(v, filter_words);
-                m[u].w[0] = ldg_na_u32(reinterpret_cast<const uint32_t *>(P.filter) + w, pol);
+                const uint32_t *ap = reinterpret_cast<const uint32_t *>(P.filter) + w;
+                uint32_t x;
+                if (mode == 1) x = ldg_na_u32(ap, pol);
+                else if (mode == 2) asm volatile("ld.global.u32 %0, [%1];" : "=r"(x) : "l"(ap));
+                else if (mode == 3) asm volatile("ld.global.cg.u32 %0, [%1];" : "=r"(x) : "l"(ap));
+                else if (mode == 4) asm volatile("ld.global.cv.u32 %0, [%1];" : "=r"(x) : "l"(ap));
+                else if (mode == 5) asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(x) : "l"(ap));
+                else if (mode == 6) asm volatile("ld.global.nc.L1::no_allocate.L2::64B.u32 %0, [%1];" : "=r"(x) : "l"(ap));
+                else if (mode == 7) asm volatile("ld.global.L1::evict_first.L2::cache_hint.u32 %0, [%1], %2;" : "=r"(x) : "l"(ap), "l"(l2_policy_evict_first()));
+                else asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(x) : "l"(ap));
+                m[u].w[0] = x;
 #pragma unroll
                 for (int j = 1; j < ModeTraits<MODE>::NW; ++j) m[u].w[j] = 0;
             }
