@@ -16,7 +16,7 @@ u8, u16, u32, u64, i32, f32, f64, vp = C.c_uint8, C.c_uint16, C.c_uint32, C.c_ui
 
 class BuildDesc(C.Structure):
     _fields_ = [("kmer_size", u8), ("window_size", u8), ("hash_funs", u32), ("max_fpr", f64), ("max_bits", u64), ("bases", vp),
-                ("rec_off", vp), ("rec_bin", vp), ("n_records", u32), ("bins", u32), ("ncat", u16), ("bin_to_cat", vp)]
+                ("rec_off", vp), ("rec_bin", vp), ("n_records", u32), ("bins", u32), ("ncat", u16), ("bin_to_cat", vp), ("force_max_hashes", u64)]
 
 
 class IndexDesc(C.Structure):
@@ -62,7 +62,7 @@ class Info(C.Structure):
 EXPORTS = ["cg_create", "cg_build_index", "cg_destroy", "cg_last_error", "cg_set_stream", "cg_sync", "cg_set_model", "cg_count_batch", "cg_eval_batch",
            "cg_classify_batch", "cg_stage_batch", "cg_run_staged", "cg_fetch_staged", "cg_get_info", "cg_host_alloc", "cg_host_free", "cg_timer_start", "cg_timer_stop", "cg_debug_minimisers",
            "cg_debug_query", "cg_debug_dump_filter", "cg_debug_force_generic", "cg_create_partitioned", "cg_partition_from_replicated",
-           "cg_partition_export", "cg_partition_attach_ipc", "cg_partition_attach_peer", "cg_bench_gather", "cg_submit_batch", "cg_wait_batch"]
+           "cg_partition_export", "cg_partition_attach_ipc", "cg_partition_attach_peer", "cg_bench_gather", "cg_submit_batch", "cg_wait_batch", "cg_export_sd_vector"]
 
 _lib = None
 
@@ -86,6 +86,7 @@ def load_library():
     L.cg_partition_attach_peer.argtypes = [vp, u32, vp]
     L.cg_submit_batch.argtypes = [vp, i32, P(Batch), P(ReadScalars), P(CountsOut), P(CallsOut)]
     L.cg_wait_batch.argtypes = [vp, i32]
+    L.cg_export_sd_vector.argtypes = [vp, P(u64), P(C.c_uint8), P(u64), P(u64), vp, vp]
     L.cg_bench_gather.argtypes = [vp, u64, i32, i32, P(f32)]
     L.cg_destroy.argtypes = [vp]; L.cg_destroy.restype = None
     L.cg_last_error.argtypes = [vp]; L.cg_last_error.restype = C.c_char_p
@@ -182,7 +183,7 @@ class GpuClassifier:
         cat = np.ascontiguousarray(np.concatenate(records)) if len(records) > 1 else np.ascontiguousarray(records[0], dtype=np.uint8)
         off = np.zeros(len(records) + 1, dtype=np.uint64); off[1:] = np.cumsum([len(r) for r in records])
         rb = np.ascontiguousarray(rec_bin, dtype=np.uint32); b2c = np.ascontiguousarray(bin_to_cat, dtype=np.uint8)
-        d = BuildDesc(k, w, hash_funs, max_fpr, 0, cat.ctypes.data, off.ctypes.data, rb.ctypes.data, len(records), len(b2c), ncat, b2c.ctypes.data)
+        d = BuildDesc(k, w, hash_funs, max_fpr, 0, cat.ctypes.data, off.ctypes.data, rb.ctypes.data, len(records), len(b2c), ncat, b2c.ctypes.data, 0)
         hpb = np.zeros(len(b2c), np.uint64)
         h = vp()
         rc = L.cg_build_index(device, C.byref(d), mem_budget, hpb.ctypes.data, C.byref(h))
@@ -384,6 +385,14 @@ class GpuClassifier:
         ms = f32(0)
         self._check(self._L.cg_bench_gather(self._h, int(n_values), mode, reps, C.byref(ms)), "cg_bench_gather")
         return float(ms.value)
+
+    def export_sd_vector(self):
+        """(size_bits, wl, low words, low_bits, high words, high_bits) of the filter as sdsl::sd_vector parts (cg_export_sd_vector)."""
+        size, wl, lb, hb = u64(0), C.c_uint8(0), u64(0), u64(0)
+        self._check(self._L.cg_export_sd_vector(self._h, C.byref(size), C.byref(wl), C.byref(lb), C.byref(hb), None, None), "cg_export_sd_vector")
+        low = np.zeros((lb.value + 63) // 64 + 1, np.uint64); high = np.zeros((hb.value + 63) // 64, np.uint64)
+        self._check(self._L.cg_export_sd_vector(self._h, C.byref(size), C.byref(wl), C.byref(lb), C.byref(hb), low.ctypes.data, high.ctypes.data), "cg_export_sd_vector")
+        return size.value, wl.value, low, lb.value, high, hb.value
 
     def timer_start(self):
         self._check(self._L.cg_timer_start(self._h), "cg_timer_start")

@@ -109,6 +109,32 @@ __global__ void sd_decode_kernel(const SdDecodeParams P) {
     }
 }
 
+// ---- compacted filter -> sdsl::sd_vector parts (what Index::serialize stores, include/index.hpp:50,130) ----
+// compact bit c = row << row_shift | bin  <->  seqan3 position row * technical_bins + bin; the mapping is monotone, so the
+// j-th set bit of the compact filter is the j-th one of the sd_vector.  prefix = exclusive popcount scan of the words.
+__global__ void sd_encode_kernel(const uint64_t *__restrict__ filter, uint64_t nwords, const uint64_t *__restrict__ prefix, uint32_t row_shift,
+                                 uint32_t technical_bins, uint32_t wl, unsigned long long *__restrict__ low, unsigned long long *__restrict__ high) {
+    const uint64_t lowmask = wl >= 64 ? ~0ull : ((1ull << wl) - 1ull);
+    for (uint64_t wi = blockIdx.x * uint64_t(blockDim.x) + threadIdx.x; wi < nwords; wi += uint64_t(gridDim.x) * blockDim.x) {
+        uint64_t w = filter[wi];
+        uint64_t j = prefix[wi];
+        while (w) {
+            const uint64_t c = wi * 64 + uint64_t(__ffsll((long long)w) - 1);
+            w &= w - 1;
+            const uint64_t row = c >> row_shift, bin = c & ((1ull << row_shift) - 1ull);
+            const uint64_t pos = row * technical_bins + bin;
+            if (wl) {
+                const uint64_t p = j * wl, v = pos & lowmask;
+                atomicOr(&low[p >> 6], v << (p & 63));
+                if ((p & 63) + wl > 64) atomicOr(&low[(p >> 6) + 1], v >> (64 - (p & 63)));
+            }
+            const uint64_t hb = (pos >> wl) + j;
+            atomicOr(&high[hb >> 6], 1ull << (hb & 63));
+            ++j;
+        }
+    }
+}
+
 // seqan3 interleaved_bloom_filter::emplace(value, bin) for an array of values (reference src/index_main.cpp:252-254)
 __global__ void ibf_insert_kernel(const uint64_t *__restrict__ values, uint64_t n, uint32_t bin, uint64_t bin_size, uint32_t hash_shift,
                                   uint32_t hash_funs, uint32_t row_shift, void *filter) {

@@ -162,4 +162,5 @@ private:
 
 }  // namespace charon_host
 
+#include "index_main.inc"
 #include "runner_impl.inc"

@@ -137,6 +137,8 @@ typedef struct cg_build_desc {
     uint32_t bins;
     uint16_t ncat;
     const uint8_t *bin_to_cat;
+    uint64_t force_max_hashes;       /* 0: size the filter for the largest bin's distinct hash count (src/index_main.cpp:239-240);
+                                        else use this count (--optimize sums per-file counts of merged bins, :192-201) */
 } cg_build_desc;
 
 /* ---- lifetime -------------------------------------------------------------------------- */
@@ -163,6 +165,12 @@ int cg_partition_export(cg_handle *h, void *ipc_handle_64);
 int cg_partition_attach_ipc(cg_handle *h, uint32_t peer_part, const void *ipc_handle_64);
 /* Peer handle living in the SAME process (one host thread per GPU): enables peer access and uses its pointer. */
 int cg_partition_attach_peer(cg_handle *h, uint32_t peer_part, cg_handle *peer);
+
+/* `charon index` output path (include/store_index.hpp:12-17, include/index.hpp:50): the filter Elias-Fano encoded ON the
+ * device into the two arrays sdsl::sd_vector serialises (m_low: low_bits/wl values of wl bits; m_high: high_bits bits).
+ * First call with low_out = high_out = NULL for the sizes, then with buffers of ceil(bits/64) words each. */
+int cg_export_sd_vector(cg_handle *h, uint64_t *size_bits, uint8_t *wl, uint64_t *low_bits, uint64_t *high_bits,
+                        uint64_t *low_out, uint64_t *high_out);
 
 void cg_destroy(cg_handle *h);
 const char *cg_last_error(const cg_handle *h);

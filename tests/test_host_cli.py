@@ -296,3 +296,75 @@ def test_dehost_two_gpus_same_bytes(charon, small_index, tmp_path, extra):
     got = run(charon, "dehost", fq, "--db", idx_path, "--gpus", "2", "--batch_reads", "60", *extra, cwd=tmp_path)
     assert got.returncode == 0, got.stderr
     assert got.stdout == want
+
+
+def _write_fasta(path, records, width=70):
+    with open(path, "w") as f:
+        for name, seq in records:
+            f.write(f">{name}\n")
+            for o in range(0, len(seq), width):
+                f.write(seq[o:o + width] + "\n")
+
+
+@pytest.mark.gpu
+def test_charon_index_writes_the_same_filter_as_the_oracle(charon, tmp_path):
+    """`charon index` (GPU hashing, distinct counts, insertion, Elias-Fano encoding) -> .idx; reloaded by the oracle's reader it
+    must hold exactly the bits and statistics of the oracle's restatement of src/index_main.cpp on the same files."""
+    from tools import synth
+    lens = [(90_000, 30_000), (120_000,), (50_000, 20_000, 10_000)]
+    cats = ["host", "microbial", "microbial"]
+    seqs, lines = [], []
+    for b, parts in enumerate(lens):
+        recs = [(f"chr{b}_{j}", synth.reference(300 + 10 * b + j, n).tobytes().decode()) for j, n in enumerate(parts)]
+        p = str(tmp_path / f"ref{b}.fa")
+        _write_fasta(p, recs)
+        seqs.append([s for _, s in recs])
+        lines.append(f"{p}\t{cats[b]}")
+    tab = tmp_path / "input.tsv"
+    tab.write_text("\n".join(lines) + "\n")
+    r = run(charon, "index", str(tab), "-p", str(tmp_path / "mine"), cwd=tmp_path)
+    assert r.returncode == 0, r.stderr
+    got = oracle.Index.load(str(tmp_path / "mine.idx"))
+    records = [np.frombuffer(s.encode(), np.uint8) for rs in seqs for s in rs]
+    rec_bin = [b for b, rs in enumerate(seqs) for _ in rs]
+    want = oracle.Index.build(records, rec_bin=rec_bin, bin_cat=[0, 1, 1], categories=["host", "microbial"])
+    assert (got.k, got.w, got.bins, got.bin_size, got.hash_funs) == (want.k, want.w, want.bins, want.bin_size, want.hash_funs)
+    assert np.array_equal(got.rows(), want.rows())
+    assert list(got.bin_to_cat) == [0, 1, 1]
+    insp = run(charon, "inspect", str(tmp_path / "mine.idx"))
+    assert insp.returncode == 0, insp.stderr
+    # and the product reads its own file: dehost against the oracle on the oracle's own index
+    reads = _mixed_reads([np.frombuffer(s.encode(), np.uint8) for s in (seqs[0][0], seqs[1][0])], 120, seed=33, min_len=300, max_len=2500)
+    fq = str(tmp_path / "r.fq")
+    _write_fastq(fq, reads)
+    out = run(charon, "dehost", fq, "--db", str(tmp_path / "mine.idx"), cwd=tmp_path)
+    assert out.returncode == 0, out.stderr
+    assert out.stdout == _oracle_tsv(want, [(x,) for x in reads], oracle.default_options(True))
+
+
+@pytest.mark.gpu
+def test_charon_index_optimize_merges_bins(charon, tmp_path):
+    from tools import synth
+    sizes = [100_000, 20_000, 15_000, 10_000, 60_000]
+    cats = ["host", "microbial", "microbial", "microbial", "host"]
+    lines = []
+    for b, n in enumerate(sizes):
+        p = str(tmp_path / f"g{b}.fasta")
+        _write_fasta(p, [(f"g{b}", synth.reference(500 + b, n).tobytes().decode())])
+        lines.append(f"{p}\t{cats[b]}")
+    tab = tmp_path / "in.tsv"
+    tab.write_text("\n".join(lines) + "\n")
+    assert run(charon, "index", str(tab), cwd=tmp_path).returncode == 0          # default output <input>.idx
+    plain = oracle.Index.load(str(tab) + ".idx")
+    r = run(charon, "index", str(tab), "-p", str(tmp_path / "opt"), "--optimize", cwd=tmp_path)
+    assert r.returncode == 0, r.stderr
+    opt = oracle.Index.load(str(tmp_path / "opt.idx"))
+    assert plain.bins == 5 and opt.bins < plain.bins                              # the three small microbial files share buckets
+    assert sorted(set(opt.bin_to_cat)) == [0, 1]
+    # merged filter answers "present" wherever any merged bin did: per category the OR of the plain masks
+    vals = oracle.minimisers(synth.reference(501, 20_000), 19, 41)[:2000]
+    pm, om = plain.query(vals)[:, 0], opt.query(vals)[:, 0]
+    for c in (0, 1):
+        pbits = sum(1 << b for b in range(plain.bins) if plain.bin_to_cat[b] == c)
+        obits = sum(1 << b for b in range(opt.bins) if opt.bin_to_cat[b] == c)
+        assert np.all(((pm & np.uint64(pbits)) != 0) <= ((om & np.uint64(obits)) != 0))
