@@ -62,7 +62,7 @@ class Info(C.Structure):
 EXPORTS = ["cg_create", "cg_build_index", "cg_destroy", "cg_last_error", "cg_set_stream", "cg_sync", "cg_set_model", "cg_count_batch", "cg_eval_batch",
            "cg_classify_batch", "cg_stage_batch", "cg_run_staged", "cg_fetch_staged", "cg_get_info", "cg_host_alloc", "cg_host_free", "cg_timer_start", "cg_timer_stop", "cg_debug_minimisers",
            "cg_debug_query", "cg_debug_dump_filter", "cg_debug_force_generic", "cg_create_partitioned", "cg_partition_from_replicated",
-           "cg_partition_export", "cg_partition_attach_ipc", "cg_partition_attach_peer", "cg_bench_gather", "cg_submit_batch", "cg_wait_batch", "cg_export_sd_vector"]
+           "cg_partition_export", "cg_partition_attach_ipc", "cg_partition_attach_peer", "cg_bench_gather", "cg_submit_batch", "cg_wait_batch", "cg_export_sd_vector", "cg_select_slot"]
 
 _lib = None
 
@@ -86,6 +86,7 @@ def load_library():
     L.cg_partition_attach_peer.argtypes = [vp, u32, vp]
     L.cg_submit_batch.argtypes = [vp, i32, P(Batch), P(ReadScalars), P(CountsOut), P(CallsOut)]
     L.cg_wait_batch.argtypes = [vp, i32]
+    L.cg_select_slot.argtypes = [vp, i32]
     L.cg_export_sd_vector.argtypes = [vp, P(u64), P(C.c_uint8), P(u64), P(u64), vp, vp]
     L.cg_bench_gather.argtypes = [vp, u64, i32, i32, P(f32)]
     L.cg_destroy.argtypes = [vp]; L.cg_destroy.restype = None
@@ -348,6 +349,9 @@ class GpuClassifier:
             self._inflight = {}
         self._inflight[slot] = (b, keep, sc, keep2, co, ca, res)   # host buffers must outlive the wait
         return res
+
+    def select_slot(self, slot):
+        self._check(self._L.cg_select_slot(self._h, slot), "cg_select_slot")
 
     def wait(self, slot):
         self._check(self._L.cg_wait_batch(self._h, slot), "cg_wait_batch")

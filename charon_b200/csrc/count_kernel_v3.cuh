@@ -35,7 +35,12 @@ template <int KK, int WW, bool SMALL> struct V3Cfg {
 };
 
 template <int MODE, int KK, int WW, bool SMALL>
-__global__ void __launch_bounds__(WARPS3 * 32, CG_V3_MINB) count_kernel_v3(const CountParams P) {
+#ifdef CG_V3_MAXNREG
+__global__ void __maxnreg__(CG_V3_MAXNREG)
+#else
+__global__ void __launch_bounds__(WARPS3 * 32, CG_V3_MINB)
+#endif
+count_kernel_v3(const CountParams P) {
     using C2 = V2Cfg<KK, WW>;
     using C = V3Cfg<KK, WW, SMALL>;
     constexpr int NW = ModeTraits<MODE>::NW;

@@ -200,6 +200,8 @@ int cg_classify_batch(cg_handle *h, const cg_batch *batch, const cg_read_scalars
 int cg_submit_batch(cg_handle *h, int slot, const cg_batch *batch, const cg_read_scalars *scalars,
                     const cg_counts_out *counts_out, const cg_calls_out *calls_out);
 int cg_wait_batch(cg_handle *h, int slot);
+/* Make `slot` the one the staged calls below (and the synchronous calls above) operate on. */
+int cg_select_slot(cg_handle *h, int slot);
 
 /* ---- staged (device-resident) variant used to time the kernels without PCIe -------------- */
 int cg_stage_batch(cg_handle *h, const cg_batch *batch, const cg_read_scalars *scalars);  /* H2D only */
