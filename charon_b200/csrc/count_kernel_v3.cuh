@@ -228,12 +228,9 @@ count_kernel_v3(const CountParams P) {
                             const uint64_t f = (uint64_t(Hi) * C2::P_KL + Lo) ^ seed, rc = (uint64_t(RHi) * C2::P_KL + RLo) ^ seed;
                             v[j] = umin64(f, rc);
                         }
-                        if (nk < uint32_t(C::NK)) {   // warp-uniform: only the last tile of a segment has k-mers past its end
-                            if (!full) {
-#pragma unroll
-                                for (int j = 0; j < WW; ++j) if (k0 + j >= nk) v[j] = VMAX;
-                            }
-                        }
+                        // k-mers at or beyond nk are NOT masked: every valid window w < Tw = nk - WW + 1 only covers k-mers
+                        // w .. w+WW-1 <= nk-1 (own suffix + the right neighbour's prefix up to that index), the tie flags below
+                        // are guarded, and windows >= Tw are dropped by the EDGE variant of p2_block / by exact_tile's bound.
                         uint64_t pm = v[0];
                         S.arr[k0] = pm;
 #pragma unroll
