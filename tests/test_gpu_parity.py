@@ -298,3 +298,74 @@ def test_two_slot_pipeline_matches_the_oracle():
     # the synchronous call still works afterwards
     common.assert_parity(gpu.classify_batch(*batches[0]), want[0])
     gpu.close()
+
+
+def test_elias_fano_encode_decode_round_trip(small):
+    """cg_export_sd_vector (device encoder, `charon index` output) -> CG_FILTER_SD_VECTOR (device decoder, `.idx` input):
+    the filter must come back bit for bit, and the parts must satisfy sdsl::sd_vector's invariants."""
+    import charon_b200
+    idx, refs, gpu = small
+    size, wl, low, low_bits, high, high_bits = gpu.export_sd_vector()
+    ones = int(np.unpackbits(idx.rows().view(np.uint8)).sum())
+    assert size == 64 * idx.bin_size and low_bits == ones * wl
+    assert int(np.unpackbits(high.view(np.uint8)).sum()) == ones
+    logm = max(ones, 1).bit_length(); logn = size.bit_length()
+    if logm == logn:
+        logm -= 1
+    assert wl == logn - logm and high_bits == ones + (1 << logm)
+    again = charon_b200.GpuClassifier(k=idx.k, w=idx.w, bins=idx.bins, bin_size=idx.bin_size, hash_funs=idx.hash_funs, bin_to_cat=idx.bin_to_cat,
+                                      ncat=idx.ncat, sd=(low, low_bits, high, high_bits, wl))
+    assert np.array_equal(again.debug_dump_filter(), idx.rows())
+    again.close()
+
+
+def test_gather_microbenchmark_runs(small):
+    idx, refs, gpu = small
+    for mode in (0, 1):
+        assert gpu.bench_gather(1_000_000, mode=mode, reps=2) > 0.0
+
+
+def test_full_size_batch_properties():
+    """BASELINE config 1 shape at a size the oracle cannot replay in seconds (2 x 200 Mbp index built on the GPU, 131 072 reads
+    of 8 kb): size-independent properties of the path + an oracle spot check on the oracle's own full-size index."""
+    import charon_b200
+    from tools import synth
+    refs = [synth.reference(1000 + b, 200_000_000) for b in range(2)]
+    gpu = charon_b200.GpuClassifier.from_references(refs, [0, 1], [0, 1], 2)
+    gpu.set_model(charon_b200.DehostOptions(), host_index=0)
+    n, L = 131_072, 8000
+    bases, src = synth.reads(42, refs, [0.45, 0.45], n, L, 0.02)
+    seg_off = np.arange(n + 1, dtype=np.uint64) * np.uint64(L)
+    mq, cr, ln = np.full(n, 20.0, np.float32), np.full(n, 0.3, np.float32), np.full(n, L, np.uint32)
+    whole = gpu.classify_batch(bases, seg_off, mq, cr, ln)
+    # (1) plausibility of the whole batch: emission density of iid sequence, reads classified to their source
+    dens = whole["num_hashes"].astype(np.float64).mean() / L
+    assert 0.085 < dens < 0.095
+    assert ((whole["call"] == src) | (src == 2))[whole["call"] != 255].mean() > 0.999
+    assert (whole["call"] != 255).mean() > 0.85
+    # (2) a batch is the concatenation of its parts: any split gives the same rows
+    cut = 50_001
+    a = gpu.classify_batch(bases[:cut * L], seg_off[:cut + 1], mq[:cut], cr[:cut], ln[:cut])
+    b = gpu.classify_batch(bases[cut * L:], seg_off[cut:] - seg_off[cut], mq[cut:], cr[cut:], ln[cut:])
+    for key in ("num_hashes", "counts", "unique_counts", "call", "confidence", "prob"):
+        assert np.array_equal(np.concatenate([a[key], b[key]]), whole[key]), key
+    # (3) order of reads does not matter
+    perm = np.random.default_rng(3).permutation(n)
+    shuffled = bases.reshape(n, L)[perm].reshape(-1)
+    p = gpu.classify_batch(shuffled, seg_off, mq, cr, ln)
+    for key in ("num_hashes", "counts", "unique_counts", "call", "confidence"):
+        assert np.array_equal(p[key], whole[key][perm]), key
+    # (4) paired reads: mates are hashed separately and pooled -> totals add (one bin per category: counts are plain sums)
+    m = 20_000
+    read_seg = np.arange(0, 2 * m + 1, 2, dtype=np.uint32)
+    pair = gpu.count_batch(bases[:2 * m * L], seg_off[:2 * m + 1], read_seg=read_seg)
+    for key in ("num_hashes", "counts", "unique_counts"):
+        w = whole[key][:2 * m]
+        assert np.array_equal(pair[key], w[0::2] + w[1::2]), key
+    # (5) oracle spot check at full index size (the oracle builds its own 2 x 200 Mbp index)
+    idx = oracle.Index.build(refs, rec_bin=[0, 1], bin_cat=[0, 1], categories=["host", "microbial"])
+    assert idx.bin_size == gpu.bin_size
+    k = 2000
+    want = idx.classify_batch(bases[:k * L], seg_off[:k + 1], mean_q=mq[:k], compression=cr[:k])
+    common.assert_parity({key: whole[key][:k] for key in ("num_hashes", "counts", "unique_counts", "call", "confidence", "prob")}, want)
+    gpu.close()
