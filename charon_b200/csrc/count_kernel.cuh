@@ -169,28 +169,35 @@ __device__ __noinline__ Mask<ModeTraits<MODE>::NW> bulk_contains_partitioned(con
     return acc;
 }
 
+template <int MODE, int NH>
+__device__ __forceinline__ Mask<ModeTraits<MODE>::NW> bulk_contains_n(const CountParams &P, uint64_t value, uint64_t pol) {
+    constexpr int NW = ModeTraits<MODE>::NW;
+    uint64_t rows[NH];
+#pragma unroll
+    for (int i = 0; i < NH; ++i) rows[i] = ibf_row(value, c_ibf_seeds[i], P.hash_shift, P.bin_size);
+    Mask<NW> r[NH];
+#pragma unroll
+    for (int i = 0; i < NH; ++i) r[i] = fetch_row<MODE>(P.filter, rows[i], P.row_shift, pol);   // all loads in flight before the AND
+    Mask<NW> acc = r[0];
+#pragma unroll
+    for (int i = 1; i < NH; ++i) {
+#pragma unroll
+        for (int j = 0; j < NW; ++j) acc.w[j] &= r[i].w[j];
+    }
+    return acc;
+}
+
 template <int MODE>
 __device__ __forceinline__ Mask<ModeTraits<MODE>::NW> bulk_contains(const CountParams &P, uint64_t value, uint64_t pol) {
-    constexpr int NW = ModeTraits<MODE>::NW;
     if (P.n_parts) return bulk_contains_partitioned<MODE>(P, value, pol);
-    Mask<NW> acc;
-    uint64_t rows[5];
-#pragma unroll
-    for (int i = 0; i < 5; ++i)
-        if (i < int(P.hash_funs)) rows[i] = ibf_row(value, c_ibf_seeds[i], P.hash_shift, P.bin_size);
-    Mask<NW> r[5];
-#pragma unroll
-    for (int i = 0; i < 5; ++i)
-        if (i < int(P.hash_funs)) r[i] = fetch_row<MODE>(P.filter, rows[i], P.row_shift, pol);   // all loads in flight before the AND
-#pragma unroll
-    for (int j = 0; j < NW; ++j) acc.w[j] = ~uint64_t(0);
-#pragma unroll
-    for (int i = 0; i < 5; ++i)
-        if (i < int(P.hash_funs)) {
-#pragma unroll
-            for (int j = 0; j < NW; ++j) acc.w[j] &= r[i].w[j];
-        }
-    return acc;
+    // `charon index` always writes 3 hash functions (include/index_arguments.hpp:21); the others only exist for foreign indexes
+    switch (P.hash_funs) {
+        case 3: return bulk_contains_n<MODE, 3>(P, value, pol);
+        case 1: return bulk_contains_n<MODE, 1>(P, value, pol);
+        case 2: return bulk_contains_n<MODE, 2>(P, value, pol);
+        case 4: return bulk_contains_n<MODE, 4>(P, value, pol);
+        default: return bulk_contains_n<MODE, 5>(P, value, pol);
+    }
 }
 
 struct Smem {

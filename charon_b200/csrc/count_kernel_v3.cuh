@@ -239,7 +239,7 @@ count_kernel_v3(const CountParams P) {
                                 tie = tie | (lo32(vleft) == lo32(pm));
                                 m_prevwin = umin64(vleft, pm);
                             }
-                            tie = tie | ((lo32(v[j]) == lo32(pm)) & (full || k0 + j < nk));
+                            tie = tie | (lo32(v[j]) == lo32(pm));   // k-mers past nk can only add a spurious exact-path tile
                             pm = umin64(pm, v[j]);
                             S.arr[k0 + j] = pm;
                         }
