@@ -29,7 +29,10 @@ template <int KK, int WW, bool SMALL> struct V3Cfg {
     static constexpr int NCNT = SMALL ? 8 : 256;
     static constexpr int CODES = ((32 + 16 * NVL * 32 + 64) + 15) / 16 * 16;
     static constexpr int RAW = NVL * 32 * 16;     // cp.async staging of the next tile's ASCII bases
-    static constexpr size_t WARP_BYTES = size_t(NK) * 8 + size_t(32) * PRIV_CAP * 8 + size_t(WLIST_CAP) * 8 + size_t(NCNT) * 8 + 32 +
+    // a lane that overruns its PRIV_CAP slots (such a tile is redone exactly) spills into its right neighbour's slots; lane 31
+    // spills into PRIV_GUARD, never into the list, whose head holds minimisers still waiting for a full gather group
+    static constexpr int PRIV_GUARD = WW + 1 - PRIV_CAP > 0 ? WW + 1 - PRIV_CAP : 0;
+    static constexpr size_t WARP_BYTES = size_t(NK) * 8 + (size_t(32) * PRIV_CAP + PRIV_GUARD) * 8 + size_t(WLIST_CAP) * 8 + size_t(NCNT) * 8 + 32 +
                                          size_t(NCNT) * 4 * 2 + CODES + RAW;
     static constexpr size_t SMEM = 512 + WARPS3 * WARP_BYTES;
 };
@@ -54,7 +57,7 @@ count_kernel_v3(const CountParams P) {
         unsigned char *w = smem_raw + 512 + size_t(warp) * C::WARP_BYTES;
         S.arr = reinterpret_cast<uint64_t *>(w);
         S.priv = S.arr + C::NK;
-        S.list = S.priv + 32 * PRIV_CAP;
+        S.list = S.priv + 32 * PRIV_CAP + C::PRIV_GUARD;
         S.best = reinterpret_cast<unsigned long long *>(S.list + WLIST_CAP);
         S.bestmask = S.best + C::NCNT;
         S.cnt = reinterpret_cast<uint32_t *>(S.bestmask + 4);
