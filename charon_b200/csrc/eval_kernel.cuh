@@ -21,6 +21,7 @@ struct ModelDev {            // one per category, device-resident
     float h_pos, h_neg;
     float beta_pos[2], beta_neg[2];
     float gamma_pos[3], gamma_neg[3];
+    uint32_t pos_sorted, neg_sorted;   // dataset ascending (the KDEParams ctor sorts; a fitted dataset keeps training order)
 };
 
 struct EvalParams {
@@ -40,11 +41,24 @@ struct EvalParams {
     double *prob; uint8_t *call; uint8_t *confidence;
 };
 
-__device__ __forceinline__ float kde_prob(const float *__restrict__ ds, uint32_t n, float h, float x) {
+__device__ __forceinline__ float kde_z(const float *__restrict__ ds, uint32_t i, float h, float x) { return __fdiv_rn(__fsub_rn(x, ds[i]), h); }
+
+// `sorted`: ds ascending, so z_i = (x - ds[i]) / h is non-increasing in i (IEEE subtraction and division by h > 0 are monotone)
+// and the terms that survive the |z| <= 15 test form one contiguous range, found by two binary searches with the very same
+// float expression; everything outside contributes exactly +0.0f.  The range is then summed in dataset order as before.
+__device__ __forceinline__ float kde_prob(const float *__restrict__ ds, uint32_t n, float h, float x, bool sorted) {
     float total = 0.0f;
     const double inv_sqrt = 2.5066282746310002;  // sqrt(2 * 3.141592653589793238463) in double
-    for (uint32_t i = 0; i < n; ++i) {
-        const float z = __fdiv_rn(__fsub_rn(x, ds[i]), h);
+    uint32_t i0 = 0, i1 = n;
+    if (sorted && !isnan(x) && h > 0.0f) {
+        uint32_t lo = 0, hi = n;                 // first i with z_i <= 15
+        while (lo < hi) { const uint32_t mid = (lo + hi) >> 1; if (kde_z(ds, mid, h, x) > 15.0f) lo = mid + 1; else hi = mid; }
+        i0 = lo; hi = n;                         // first i with z_i < -15
+        while (lo < hi) { const uint32_t mid = (lo + hi) >> 1; if (kde_z(ds, mid, h, x) >= -15.0f) lo = mid + 1; else hi = mid; }
+        i1 = lo;
+    }
+    for (uint32_t i = i0; i < i1; ++i) {
+        const float z = kde_z(ds, i, h, x);
         if (fabsf(z) > 15.0f) continue;                                 // term rounds to exactly +0.0f
         const double zz = double(z) * double(z);                         // std::pow(float,2) -> exact in double
         const float kf = float(exp(-zz / 2.0) / inv_sqrt);
@@ -85,8 +99,8 @@ __global__ void prob_kernel(const EvalParams P) {
     const float p_err = dexp300(x, P.log_rate);
     float p_pos, p_neg;
     if (m.dist == 0) {
-        p_pos = kde_prob(P.pool + m.pos_off, m.npos, m.h_pos, x);
-        p_neg = kde_prob(P.pool + m.neg_off, m.nneg, m.h_neg, x);
+        p_pos = kde_prob(P.pool + m.pos_off, m.npos, m.h_pos, x, m.pos_sorted != 0);
+        p_neg = kde_prob(P.pool + m.neg_off, m.nneg, m.h_neg, x, m.neg_sorted != 0);
     } else if (m.dist == 2) {
         p_pos = dgamma_dev(__fsub_rn(x, m.gamma_pos[1]), m.gamma_pos[0], m.gamma_pos[2]);
         p_neg = dgamma_dev(__fsub_rn(x, m.gamma_neg[1]), m.gamma_neg[0], m.gamma_neg[2]);
