@@ -150,7 +150,9 @@ __device__ __forceinline__ void p2_block(uint64_t (&v)[WW], uint64_t vleft, cons
         const uint64_t leaving = j >= 1 ? v[j >= 1 ? j - 1 : 0] : vleft;
         tie = tie | ((lo32(leaving) == lo32(mw)) & wv);
         if (j < WW - 1) {
-            const bool start = (mw_next != mw) & (!EDGE || (k0 + j + 1 < Tw));
+            // low words suffice: two DIFFERENT adjacent window minima with equal low words always trip one of the tie flags
+            // (old minimum left: `leaving` check; newcomer took over: it met the old minimum in a prefix / suffix / combine step)
+            const bool start = (lo32(mw_next) != lo32(mw)) & (!EDGE || (k0 + j + 1 < Tw));
             if (start) { *pslot = mw_next; ++pslot; }
         }
         mw_next = mw;

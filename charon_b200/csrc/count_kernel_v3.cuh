@@ -259,7 +259,7 @@ count_kernel_v3(const CountParams P) {
                     if (active && k0 < Tw) {
                         if (k0 + WW <= Tw) p2_block<WW, false>(v, vleft, S.arr + k0 + WW, k0, Tw, pslot, tie);
                         else p2_block<WW, true>(v, vleft, S.arr + k0 + WW, k0, Tw, pslot, tie);
-                        if (k0 > 0 ? (v[0] != m_prevwin) : first) { *pslot = v[0]; ++pslot; }
+                        if (k0 > 0 ? (lo32(v[0]) != lo32(m_prevwin)) : first) { *pslot = v[0]; ++pslot; }   // low words: see p2_block
                     }
                     const uint32_t cnt = uint32_t(pslot - pslot0);
                     tie = tie | (cnt > PRIV_CAP);
