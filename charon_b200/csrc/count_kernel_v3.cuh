@@ -142,6 +142,28 @@ count_kernel_v3(const CountParams P) {
             const bool last_pass = (pass == npass - 1);
 
             uint32_t pend = 0;   // emitted values waiting at the front of S.list for a full group of 32 (warp-uniform)
+            // Deferred gathers (narrow rows, 3 hash functions, local filter): the row loads of up to DQ groups are issued at the
+            // end of a tile and consumed after the NEXT tile's hashing, so the HBM / L2 latency hides behind arithmetic.
+            constexpr int DQ = (MODE == 0) ? 3 : 0;
+            uint32_t dq_w[DQ ? DQ : 1][3], dq_sh[DQ ? DQ : 1];
+            uint32_t ndq = 0;
+            const bool can_defer = DQ && P.hash_funs == 3 && P.n_parts == 0;
+            auto dq_finish = [&]() {
+                if (DQ) {
+                    const uint32_t rb = 1u << P.row_shift;
+                    const uint32_t msk = rb >= 32 ? 0xFFFFFFFFu : ((1u << rb) - 1u);
+#pragma unroll
+                    for (int g = 0; g < DQ; ++g)
+                        if (g < int(ndq)) {
+                            Mask<NW> m;
+#pragma unroll
+                            for (int j = 1; j < NW; ++j) m.w[j] = 0;
+                            m.w[0] = ((dq_w[g][0] >> (dq_sh[g] & 31u)) & (dq_w[g][1] >> ((dq_sh[g] >> 5) & 31u)) & (dq_w[g][2] >> (dq_sh[g] >> 10))) & msk;
+                            T.add(m, bm, small_bins, do_tot, do_unq, S);
+                        }
+                }
+                ndq = 0;
+            };
             for (uint32_t seg = seg0; seg < seg1; ++seg) {
                 const uint64_t sbase = P.seg_off[seg];
                 const uint64_t slen = P.seg_len ? P.seg_len[seg] : P.seg_off[seg + 1] - sbase;
@@ -301,7 +323,27 @@ count_kernel_v3(const CountParams P) {
                     if (P.filter) {
                         // only full groups of 32 are queried now; the remainder waits for the next tile's emissions
                         const uint32_t have = pend + nl, fullg = have & ~31u;
-                        for (uint32_t i = lane; i < fullg; i += 32) {
+                        uint32_t first_now = 0;   // groups below this index go through the deferred queue
+                        if (can_defer) {
+                            dq_finish();          // loads issued one tile ago: their latency is behind us
+                            const uint32_t ngroups = fullg >> 5;
+#pragma unroll
+                            for (int g = 0; g < DQ; ++g)
+                                if (uint32_t(g) < ngroups) {
+                                    const uint64_t value = S.list[g * 32 + lane];
+                                    uint32_t sh = 0;
+#pragma unroll
+                                    for (int i = 0; i < 3; ++i) {
+                                        const uint64_t bit = ibf_row(value, c_ibf_seeds[i], P.hash_shift, P.bin_size) << P.row_shift;
+                                        dq_w[g][i] = ldg_na_u32(reinterpret_cast<const uint32_t *>(P.filter) + (bit >> 5), pol_filter);
+                                        sh |= (uint32_t(bit) & 31u) << (5 * i);
+                                    }
+                                    dq_sh[g] = sh;
+                                }
+                            ndq = ngroups < uint32_t(DQ) ? ngroups : uint32_t(DQ);
+                            first_now = ndq * 32;
+                        }
+                        for (uint32_t i = first_now + lane; i < fullg; i += 32) {
                             const Mask<NW> m = bulk_contains<MODE>(P, S.list[i], pol_filter);
                             T.add(m, bm, small_bins, do_tot, do_unq, S);
                         }
@@ -319,6 +361,7 @@ count_kernel_v3(const CountParams P) {
                     first = false;
                 }  // tiles
             }      // segments
+            dq_finish();
             if (pend) {   // flush the last partial group of this pass
                 __syncwarp();
                 if (lane < pend) {
