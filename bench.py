@@ -10,8 +10,8 @@ N > 1 (under torchrun): one rank per GPU, filter replicated, reads sharded, NO d
 is used only for the barrier and the max-over-ranks of the device-measured time ("scaling": "weak").
 
 value : whole-job reads/s with the batch already resident in HBM (CUDA events on the launching stream).
-e2e   : the same through the C-ABI call cg_classify_batch with pinned HOST buffers (H2D + kernels + D2H inside the
-        timed region).
+e2e   : the same through the C-ABI calls cg_submit_batch / cg_wait_batch with pinned ASCII HOST buffers (H2D + kernels + D2H
+        inside the timed region; with >= 8 host threads per GPU the library packs the bases to 4 bits on the way, also inside it).
 --impl reference : the reference's CPU implementation of the path = the oracle port (the real charon cannot be built
         here: its CMake downloads seqan3 & co.), all host threads, on a bounded sample of the same workload.
 """
@@ -176,6 +176,15 @@ def run_b200(args, wl):
         gpu.partition(rank, world)
         multi.exchange_partitions(gpu, dist, rank, world, device=torch.device("cuda", local_rank))
     gpu.set_model(charon_b200.DehostOptions(), host_index=0)
+    # transport of the bases over PCIe: the library packs them to 4-bit ranks on host threads when it has at least 8 of them
+    # (cg_set_host_pack); the ranks of one box share its cores
+    try:
+        host_cores = len(os.sched_getaffinity(0))
+    except AttributeError:
+        host_cores = os.cpu_count() or 1
+    pack_threads = max(1, min(16, host_cores // world))
+    pack_mode = {"auto": -1, "off": 0, "on": 1}[args.host_pack]
+    gpu.set_host_pack(pack_mode, pack_threads)
     # this rank's batch (weak scaling: R reads per GPU per step), in pinned host memory
     bases = pinned_array((R * L,), np.uint8)
     _, seg_off, _ = make_reads(wl, records, rec_bin, R, first_index=rank * R, out=bases)
@@ -222,8 +231,26 @@ def run_b200(args, wl):
     barrier()
     clocks = sampler.stop(w0, w1)
     res = gpu.fetch_staged(True)
+    resident_packed = bool(gpu.info().last_packed)
     minimisers = int(res["num_hashes"].astype(np.int64).sum())
     total_ms_max = max_over_ranks(total_ms)
+    # the same kernels on the other resident format (ASCII, one byte per base), for comparison only
+    other_value = None
+    if resident_packed:
+        gpu.set_host_pack(0, 0)
+        gpu._check(Lb.cg_stage_batch(gpu._h, C.byref(batch), C.byref(sc)), "cg_stage_batch")
+        for _ in range(args.warmup):
+            gpu.run_staged(True)
+        barrier()
+        gpu.timer_start()
+        for _ in range(args.steps):
+            gpu.run_staged(True)
+        o_ms, o_count_ms, _, o_runs = gpu.timer_stop()
+        barrier()
+        res_o = gpu.fetch_staged(True)
+        assert np.array_equal(res_o["num_hashes"], res["num_hashes"]) and np.array_equal(res_o["counts"], res["counts"]) and np.array_equal(res_o["call"], res["call"])
+        other_value = {"reads_per_sec": R * args.steps * world / (max_over_ranks(o_ms) / 1e3), "count_kernel_ms": o_count_ms / max(o_runs, 1)}
+        gpu.set_host_pack(pack_mode, 0)
     # ---- end-to-end arm: host buffers through the C-ABI (H2D + kernels + D2H of every step inside the timed region) -------
     # cg_submit_batch / cg_wait_batch on two slots: the PCIe copy of step i+1 overlaps the kernels of step i
     out2 = dict(num_hashes=pinned_array((R,), np.uint32), counts=pinned_array((R, 2), np.uint32), unique_counts=pinned_array((R, 2), np.uint32),
@@ -248,6 +275,7 @@ def run_b200(args, wl):
     e2e_ms, _, _, _ = gpu.timer_stop()
     barrier()
     e2e_ms_max = max_over_ranks(e2e_ms)
+    e2e_info = gpu.info()
     assert np.array_equal(out["num_hashes"], res["num_hashes"]) and np.array_equal(out["call"], res["call"])
     assert args.steps < 2 or (np.array_equal(out2["num_hashes"], res["num_hashes"]) and np.array_equal(out2["call"], res["call"]))
     # ---- serial variant of the same call (cg_classify_batch: copy, kernels, copy back, one after the other) -----------------
@@ -291,10 +319,14 @@ def run_b200(args, wl):
                        "filter_partitioned": partitioned, "reads_per_step_per_gpu": R, "read_len": L, "k": 19, "w": 41, "hash_funs": 3,
                        "filter_rows": int(info.bin_size), "filter_bytes_hbm": int(info.filter_bytes), "row_bits": int(info.row_bits),
                        "minimisers_per_step_per_gpu": minimisers, "classified_frac": float((res["call"] != 255).mean()),
-                       "l2_note": "step input (1 B/base x reads) is larger than the 126 MB L2 and is re-read every step; no flush needed",
+                       "l2_note": "step input (0.5 or 1 B/base x reads = 0.5 / 1 GB) is larger than the 126 MB L2 and is re-read every step; no flush needed",
+                       "hbm_resident_bases": "4-bit dna5 ranks (the library's transport format)" if resident_packed else "ASCII, 1 byte per base",
+                       "value_on_ascii_resident_bases": other_value,
                        "index_build_on_gpu_s": round(build_s, 2)},
             "gbases_per_sec": value * L / 1e9,
-            "e2e": {"value": e2e, "unit": "reads/s", "h2d_bytes_per_step": int(R * L + (R + 1) * 8 + R * 12) * world,
+            "e2e": {"value": e2e, "unit": "reads/s", "h2d_bytes_per_step": int(e2e_info.last_h2d_bytes) * world,
+                    "transport": "ASCII host buffers packed to 4-bit ranks inside the call, chunk copies overlapped" if e2e_info.last_packed else "ASCII copied as is",
+                    "host_pack_threads_per_gpu": pack_threads if e2e_info.last_packed else 0, "host_pack_ms_per_step": float(e2e_info.last_pack_ms),
                     "d2h_bytes_per_step": int(R * (4 + 8 + 8 + 16 + 2)) * world, "gbases_per_sec": e2e * L / 1e9,
                     "api": "cg_submit_batch/cg_wait_batch, two slots (copy of step i+1 overlaps kernels of step i)",
                     "serial_cg_classify_batch_value": reads_total / (serial_ms_max / 1e3)},
@@ -354,6 +386,7 @@ def main():
     ap.add_argument("--workload", default="bacterial", choices=sorted(WORKLOADS))
     ap.add_argument("--reads-per-step", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--host-pack", default="auto", choices=["auto", "on", "off"], help="transport of the bases over PCIe: 4-bit ranks packed on host threads (auto: when >= 8 threads per GPU) or ASCII")
     ap.add_argument("--partitioned", action="store_true", help="N>1: split the filter by row range across the GPUs instead of replicating it")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup

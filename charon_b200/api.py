@@ -56,13 +56,13 @@ class Info(C.Structure):
     _fields_ = [("bin_size", u64), ("filter_bytes", u64), ("row_bits", u32), ("single_pass", u32), ("sm_count", u32), ("count_grid", u32),
                 ("count_block", u32), ("count_smem_bytes", u32), ("last_minimisers", u64), ("last_bases", u64),
                 ("last_kernel_launches", u32), ("last_count_kernel_ms", f32), ("last_eval_kernel_ms", f32), ("last_h2d_ms", f32),
-                ("last_d2h_ms", f32)]
+                ("last_d2h_ms", f32), ("last_h2d_bytes", u64), ("last_pack_ms", f32), ("last_packed", u32)]
 
 
 EXPORTS = ["cg_create", "cg_build_index", "cg_destroy", "cg_last_error", "cg_set_stream", "cg_sync", "cg_set_model", "cg_count_batch", "cg_eval_batch",
            "cg_classify_batch", "cg_stage_batch", "cg_run_staged", "cg_fetch_staged", "cg_get_info", "cg_host_alloc", "cg_host_free", "cg_timer_start", "cg_timer_stop", "cg_debug_minimisers",
            "cg_debug_query", "cg_debug_dump_filter", "cg_debug_force_generic", "cg_create_partitioned", "cg_partition_from_replicated",
-           "cg_partition_export", "cg_partition_attach_ipc", "cg_partition_attach_peer", "cg_bench_gather", "cg_submit_batch", "cg_wait_batch", "cg_export_sd_vector", "cg_select_slot"]
+           "cg_partition_export", "cg_partition_attach_ipc", "cg_partition_attach_peer", "cg_bench_gather", "cg_submit_batch", "cg_wait_batch", "cg_export_sd_vector", "cg_select_slot", "cg_set_host_pack", "cg_pack_bases"]
 
 _lib = None
 
@@ -87,6 +87,8 @@ def load_library():
     L.cg_submit_batch.argtypes = [vp, i32, P(Batch), P(ReadScalars), P(CountsOut), P(CallsOut)]
     L.cg_wait_batch.argtypes = [vp, i32]
     L.cg_select_slot.argtypes = [vp, i32]
+    L.cg_set_host_pack.argtypes = [vp, i32, i32]
+    L.cg_pack_bases.argtypes = [vp, u64, vp]
     L.cg_export_sd_vector.argtypes = [vp, P(u64), P(C.c_uint8), P(u64), P(u64), vp, vp]
     L.cg_bench_gather.argtypes = [vp, u64, i32, i32, P(f32)]
     L.cg_destroy.argtypes = [vp]; L.cg_destroy.restype = None
@@ -143,6 +145,17 @@ def pinned_array(shape, dtype):
 
 
 _PINNED = {}
+
+
+def pack_bases(bases) -> np.ndarray:
+    """4-bit dna5 ranks of an ASCII base array, two per byte (cg_pack_bases: the transport the library uses on PCIe)."""
+    L = load_library()
+    b = np.ascontiguousarray(np.frombuffer(bases.encode() if isinstance(bases, str) else bases, np.uint8) if not isinstance(bases, np.ndarray) else bases, np.uint8)
+    out = np.zeros((b.size + 1) // 2, np.uint8)
+    rc = L.cg_pack_bases(b.ctypes.data_as(C.c_void_p), b.size, out.ctypes.data_as(C.c_void_p))
+    if rc:
+        raise RuntimeError(f"cg_pack_bases failed ({rc})")
+    return out
 
 
 def _ptr(a):
@@ -352,6 +365,10 @@ class GpuClassifier:
 
     def select_slot(self, slot):
         self._check(self._L.cg_select_slot(self._h, slot), "cg_select_slot")
+
+    def set_host_pack(self, mode=-1, threads=0):
+        """Transport of the bases (cg_set_host_pack): -1 automatic, 0 ASCII copies, 1 packed 4-bit ranks; threads > 0 resizes the pool."""
+        self._check(self._L.cg_set_host_pack(self._h, mode, threads), "cg_set_host_pack")
 
     def wait(self, slot):
         self._check(self._L.cg_wait_batch(self._h, slot), "cg_wait_batch")

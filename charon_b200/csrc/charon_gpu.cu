@@ -11,6 +11,7 @@
 #include <algorithm>
 #include <utility>
 #include <cmath>
+#include <chrono>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
@@ -21,6 +22,7 @@
 #include "count_kernel.cuh"
 #include "count_kernel_v2.cuh"
 #include "count_kernel_v3.cuh"
+#include "host_pack.hpp"
 #include "eval_kernel.cuh"
 #include "filter_build.cuh"
 #include "gather_bench.cuh"
@@ -80,6 +82,11 @@ struct cg_handle {
     uint32_t staged_reads = 0, staged_segs = 0;
     uint64_t staged_bases = 0;
     bool staged_has_read_seg = false, staged_has_scalars = false;
+    // packed transport (host_pack.hpp): the staged bases are 4-bit ranks; pinned staging buffer of the active slot and the
+    // event that says its last chunk has been copied out
+    bool staged_packed = false;
+    struct PackStage { void *p = nullptr; size_t cap = 0; cudaEvent_t done = nullptr; bool armed = false; } pack;
+    int host_pack_mode = -1;      // -1: automatic (thread pool of at least 8), 0: never, 1: whenever the (19, 41) kernels apply
     // launch config
     int grid_per_sm = 1;
     int warp_grid_per_sm = 1;
@@ -94,7 +101,8 @@ struct cg_handle {
         DevBuf bases, seg_off, read_seg, num_hashes, counts, unique, prob, call, conf, mq, cr, len, counter;
         uint32_t staged_reads = 0, staged_segs = 0;
         uint64_t staged_bases = 0, staged_max_read_len = 0;
-        bool staged_has_read_seg = false, staged_has_scalars = false;
+        bool staged_has_read_seg = false, staged_has_scalars = false, staged_packed = false;
+        PackStage pack;
         bool created = false, pending = false;
         cg_counts_out co{}; cg_calls_out ca{}; bool has_co = false, has_ca = false;
     } parked;
@@ -112,6 +120,7 @@ struct cg_handle {
         std::swap(staged_reads, parked.staged_reads); std::swap(staged_segs, parked.staged_segs);
         std::swap(staged_bases, parked.staged_bases); std::swap(staged_max_read_len, parked.staged_max_read_len);
         std::swap(staged_has_read_seg, parked.staged_has_read_seg); std::swap(staged_has_scalars, parked.staged_has_scalars);
+        std::swap(staged_packed, parked.staged_packed); std::swap(pack, parked.pack);
         std::swap(active_pending, parked.pending);
         std::swap(act_co, parked.co); std::swap(act_ca, parked.ca); std::swap(act_has_co, parked.has_co); std::swap(act_has_ca, parked.has_ca);
         active_slot ^= 1;
@@ -160,7 +169,7 @@ cgk::CountParams make_params(cg_handle *h) {
     P.seg_len = nullptr;
     P.long_read_min = 0; P.long_only = 0;
     P.dbg_out = nullptr; P.dbg_cap = 0; P.dbg_n = nullptr;
-    P.n_parts = h->n_parts; P.my_part = h->my_part; P.rows_per_part = h->rows_per_part; P.part_pad = 0;
+    P.n_parts = h->n_parts; P.my_part = h->my_part; P.rows_per_part = h->rows_per_part; P.packed = h->staged_packed ? 1 : 0;
     for (int i = 0; i < CG_MAX_PARTS; ++i) P.part_base[i] = h->part_base[i];
     return P;
 }
@@ -327,18 +336,53 @@ int validate_batch(cg_handle *h, const cg_batch *b) {
 }
 
 // H2D of one batch (src/dehost_main.cpp:335-339: the chunk of records handed to the loop)
+constexpr uint64_t PACK_MIN_BASES = 1u << 20, PACK_CHUNK_BASES = 32u << 20;
 int stage(cg_handle *h, const cg_batch *b, const cg_read_scalars *sc) {
     if (h->active_pending) return fail(h, CG_ERR_STATE, "a submitted batch is still in flight on this slot: cg_wait_batch first");
     int rc = validate_batch(h, b);
     if (rc) return rc;
     const uint64_t nbases = b->n_segs ? b->seg_off[b->n_segs] : 0;
-    RSV(h, h->bases, nbases + 64);
+    // Packed transport: only the (19, 41) kernels decode it; in automatic mode tiny batches are not worth waking the pool for.
+    const bool pack = use_fast(h) && nbases > 0 && (h->host_pack_mode == 1 || (h->host_pack_mode < 0 && nbases >= PACK_MIN_BASES && cgh::threads() >= 8));
+    RSV(h, h->bases, (pack ? (nbases + 1) / 2 : nbases) + 64);
     RSV(h, h->seg_off, (size_t(b->n_segs) + 1) * 8);
     if (b->read_seg) RSV(h, h->read_seg, (size_t(b->n_reads) + 1) * 4);
     rc = reserve_outputs(h, b->n_reads);
     if (rc) return rc;
-    CU(h, cudaEventRecord(h->ev[0], h->stream));
-    if (nbases) CU(h, cudaMemcpyAsync(h->bases.p, b->bases, nbases, cudaMemcpyHostToDevice, h->stream));
+    h->staged_packed = pack;
+    h->info.last_packed = pack ? 1 : 0; h->info.last_pack_ms = 0;
+    if (pack) {
+        const size_t pbytes = size_t((nbases + 1) / 2);
+        auto &ps = h->pack;
+        if (!ps.done) CU(h, cudaEventCreateWithFlags(&ps.done, cudaEventDisableTiming));
+        if (ps.armed) { CU(h, cudaEventSynchronize(ps.done)); ps.armed = false; }   // previous copy out of the staging buffer is over
+        if (ps.cap < pbytes) {
+            if (ps.p) cudaFreeHost(ps.p);
+            ps.p = nullptr; ps.cap = 0;
+            const size_t want = pbytes + pbytes / 8 + 4096;
+            CU(h, cudaHostAlloc(&ps.p, want, cudaHostAllocDefault));
+            ps.cap = want;
+        }
+        CU(h, cudaEventRecord(h->ev[0], h->stream));
+        cudaError_t ce = cudaSuccess;
+        const auto t0 = std::chrono::steady_clock::now();
+        cgh::pack_chunked(reinterpret_cast<const uint8_t *>(b->bases), static_cast<uint8_t *>(ps.p), nbases, PACK_CHUNK_BASES,
+                          [&](uint64_t lo, uint64_t hi) {   // chunk [lo, hi) is packed (lo is even): its copy overlaps the packing of the next
+                              if (ce == cudaSuccess)
+                                  ce = cudaMemcpyAsync(h->bases.as<uint8_t>() + lo / 2, static_cast<const uint8_t *>(ps.p) + lo / 2, size_t((hi - lo + 1) / 2),
+                                                       cudaMemcpyHostToDevice, h->stream);
+                          });
+        h->info.last_pack_ms = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
+        CU(h, ce);
+        CU(h, cudaEventRecord(ps.done, h->stream));
+        ps.armed = true;
+        h->info.last_h2d_bytes = pbytes;
+    } else {
+        CU(h, cudaEventRecord(h->ev[0], h->stream));
+        if (nbases) CU(h, cudaMemcpyAsync(h->bases.p, b->bases, nbases, cudaMemcpyHostToDevice, h->stream));
+        h->info.last_h2d_bytes = nbases;
+    }
+    h->info.last_h2d_bytes += (size_t(b->n_segs) + 1) * 8 + (b->read_seg ? (size_t(b->n_reads) + 1) * 4 : 0) + (sc && b->n_reads ? size_t(b->n_reads) * 12 : 0);
     static const uint64_t zero_off[1] = {0};
     CU(h, cudaMemcpyAsync(h->seg_off.p, b->n_segs ? b->seg_off : zero_off, (size_t(b->n_segs) + 1) * 8, cudaMemcpyHostToDevice, h->stream));
     if (b->read_seg) CU(h, cudaMemcpyAsync(h->read_seg.p, b->read_seg, (size_t(b->n_reads) + 1) * 4, cudaMemcpyHostToDevice, h->stream));

@@ -21,7 +21,7 @@ constexpr uint32_t INV5 = 0xCCCCCCCDu;  // 5^-1 mod 2^32 (exact division of mult
 #define CG_MAX_PARTS 16
 
 struct CountParams {
-    const uint8_t *bases;
+    const uint8_t *bases;       // ASCII, one base per byte — or, when `packed`, rank nibbles (16-byte aligned buffer)
     const uint64_t *seg_off;
     const uint32_t *read_seg;   // may be null: one segment per read
     const uint64_t *seg_len;    // may be null: segment s = [seg_off[s], seg_off[s+1]); else [seg_off[s], seg_off[s]+seg_len[s])
@@ -51,7 +51,8 @@ struct CountParams {
     // row-range partitioned filter: part p holds rows [p*rows_per_part, (p+1)*rows_per_part) in its own
     // allocation on GPU p; remote parts are NVLink peer mappings.  n_parts == 0: `filter` is the whole (replicated) filter.
     uint32_t n_parts, my_part;
-    uint32_t rows_per_part, part_pad;   // rows are < 2^32 (bin_size <= 2^32 - 3)
+    uint32_t rows_per_part;             // rows are < 2^32 (bin_size <= 2^32 - 3)
+    uint32_t packed;                    // bases are 4-bit dna5 ranks, two per byte (host_pack.hpp); only the (19, 41) kernels
     const void *part_base[CG_MAX_PARTS];
 };
 
@@ -240,7 +241,7 @@ __device__ __forceinline__ uint8_t base_code(unsigned c) {
 }
 
 template <int MODE>
-__global__ void __launch_bounds__(NT) count_kernel(const CountParams P) {
+__global__ void __launch_bounds__(NT) count_kernel(const __grid_constant__ CountParams P) {
     constexpr int NW = ModeTraits<MODE>::NW;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const Smem S = carve(smem_raw);

@@ -80,6 +80,22 @@ __device__ __forceinline__ uint32_t encode4(const uint8_t *lut, uint32_t w) {   
 }
 __device__ __forceinline__ uint64_t umin64(uint64_t a, uint64_t b) { return a < b ? a : b; }
 
+// Packed transport (host_pack.hpp): a nibble is the dna5 rank.  PRMT with the nibbles themselves as byte selectors expands
+// four bases per instruction into exactly the code bytes base_code() yields for ASCII (rank | complement rank << 4).
+constexpr uint32_t PK_TLO = 0x33122140u, PK_THI = 0x33333304u;   // code bytes of ranks 0..3 / 4..7 (5..7 never occur: N)
+__device__ __forceinline__ void decode_packed16(const uint4 x, uint4 &a, uint4 &b) {   // 32 bases -> 32 code bytes
+    a.x = __byte_perm(PK_TLO, PK_THI, x.x); a.y = __byte_perm(PK_TLO, PK_THI, x.x >> 16);
+    a.z = __byte_perm(PK_TLO, PK_THI, x.y); a.w = __byte_perm(PK_TLO, PK_THI, x.y >> 16);
+    b.x = __byte_perm(PK_TLO, PK_THI, x.z); b.y = __byte_perm(PK_TLO, PK_THI, x.z >> 16);
+    b.z = __byte_perm(PK_TLO, PK_THI, x.w); b.w = __byte_perm(PK_TLO, PK_THI, x.w >> 16);
+}
+// code byte of base i of the batch, either transport (cold paths only)
+__device__ __forceinline__ uint32_t code_at(const uint8_t *bases, bool packed, const uint8_t *lut, uint64_t i) {
+    if (!packed) return lut[bases[i]];
+    const uint32_t r = (uint32_t(bases[i >> 1]) >> ((uint32_t(i) & 1u) * 4u)) & 7u;
+    return uint32_t((((unsigned long long)PK_THI << 32) | PK_TLO) >> (8u * r)) & 0xFFu;
+}
+
 // per-read counters shared by the list phase and the inline (exact path) emission
 template <int MODE>
 struct Tally {
@@ -224,7 +240,7 @@ __device__ __noinline__ void exact_tile(const CountParams &P, const Smem2 &S, ui
 }
 
 template <int MODE, int KK, int WW>
-__global__ void __launch_bounds__(NT2, CG_V2_MINB) count_kernel_v2(const CountParams P) {
+__global__ void __launch_bounds__(NT2, CG_V2_MINB) count_kernel_v2(const __grid_constant__ CountParams P) {
     using C = V2Cfg<KK, WW>;
     constexpr int NW = ModeTraits<MODE>::NW;
     constexpr int KL = C::KL, KH = C::KH;
@@ -280,16 +296,13 @@ __global__ void __launch_bounds__(NT2, CG_V2_MINB) count_kernel_v2(const CountPa
                         uint64_t best = VMAX;
                         for (uint32_t i = lane; i < nkm; i += 32) {
                             uint64_t f = 0, rc = 0;
-                            for (int j = 0; j < KK; ++j) {
-                                const uint32_t c = S.lut[P.bases[sbase + i + j]];
-                                f = f * 5u + (c & 15u);
-                            }
-                            for (int j = KK; j-- > 0;) rc = rc * 5u + (S.lut[P.bases[sbase + i + j]] >> 4);
+                            for (int j = 0; j < KK; ++j) f = f * 5u + (code_at(P.bases, P.packed != 0, S.lut, sbase + i + j) & 15u);
+                            for (int j = KK; j-- > 0;) rc = rc * 5u + (code_at(P.bases, P.packed != 0, S.lut, sbase + i + j) >> 4);
                             best = umin64(best, umin64(f ^ seed, rc ^ seed));
                         }
 #pragma unroll
                         for (int o = 16; o > 0; o >>= 1) best = umin64(best, __shfl_xor_sync(0xFFFFFFFFu, best, o));
-                        if (lane == 0) process_exact<MODE>(P, S, &s_nhash, best, do_tot, do_unq);
+                        if (lane == 0) { const Smem2 Sx = S; process_exact<MODE>(P, Sx, &s_nhash, best, do_tot, do_unq); }
                     }
                     continue;
                 }
@@ -302,9 +315,19 @@ __global__ void __launch_bounds__(NT2, CG_V2_MINB) count_kernel_v2(const CountPa
                     const uint32_t nb = nk + KK - 1;
                     // ---- phase 0: load + encode.  16-byte vectors aligned in GLOBAL memory, all of a thread's loads in
                     //      flight before the first use; codes[32 + head + i] = code of tile base i -----------------
-                    const uint8_t *gsrc = P.bases + sbase + g0;
-                    const uint32_t head = uint32_t(reinterpret_cast<uintptr_t>(gsrc) & 15u);
-                    {
+                    const uint64_t G = sbase + g0;   // index of the tile's first base in the batch
+                    const uint8_t *gsrc = P.bases + G;
+                    const uint32_t head = P.packed ? uint32_t(G & 31u) : uint32_t(reinterpret_cast<uintptr_t>(gsrc) & 15u);
+                    if (P.packed) {   // 16-byte vectors of 32 rank nibbles; one vector per thread covers a tile
+                        const uint4 *vsrc = reinterpret_cast<const uint4 *>(P.bases) + (G >> 5);
+                        const uint32_t nvec = (head + nb + 31u) >> 5;
+                        if (tid < nvec) {
+                            uint4 a, b;
+                            decode_packed16(ldg_stream_v4(vsrc + tid, pol_stream), a, b);
+                            *reinterpret_cast<uint4 *>(S.codes + 32 + 32 * tid) = a;
+                            *reinterpret_cast<uint4 *>(S.codes + 32 + 32 * tid + 16) = b;
+                        }
+                    } else {
                         const uint4 *vsrc = reinterpret_cast<const uint4 *>(gsrc - head);
                         const uint32_t nvec = (head + nb + 15u) >> 4;
                         constexpr int NV = (C::NB + 15 + 15) / 16 / NT2 + 1;   // vectors per thread (2 for k=19, w=41)
@@ -422,7 +445,7 @@ __global__ void __launch_bounds__(NT2, CG_V2_MINB) count_kernel_v2(const CountPa
                         __syncthreads();
                         if (tid == 0) s_carry_valid = 0;     // re-armed by the walker of the run alive at the last window
                         __syncthreads();
-                        exact_tile<MODE, WW>(P, S, &s_nhash, &s_carry_pos, &s_carry_valid, Tw, first, carry, g0, do_tot, do_unq);
+                        { const Smem2 Sx = S; exact_tile<MODE, WW>(P, Sx, &s_nhash, &s_carry_pos, &s_carry_valid, Tw, first, carry, g0, do_tot, do_unq); }
                         nl = 0;
                         __syncthreads();
                     } else if (tid == 0) {

@@ -28,7 +28,8 @@ template <int KK, int WW, bool SMALL> struct V3Cfg {
     static constexpr int NVL = (NVEC + 31) / 32;          // vectors per lane
     static constexpr int NCNT = SMALL ? 8 : 256;
     static constexpr int CODES = ((32 + 16 * NVL * 32 + 64) + 15) / 16 * 16;
-    static constexpr int RAW = NVL * 32 * 16;     // cp.async staging of the next tile's ASCII bases
+    static constexpr int RAW = NVL * 32 * 16;     // cp.async staging of the next tile's bases (ASCII, or 32 rank nibbles per vector)
+    static_assert((31 + NB + 31) / 32 <= 32, "packed transport: one vector per lane must cover a tile");
     // a lane that overruns its PRIV_CAP slots (such a tile is redone exactly) spills into its right neighbour's slots; lane 31
     // spills into PRIV_GUARD, never into the list, whose head holds minimisers still waiting for a full gather group
     static constexpr int PRIV_GUARD = WW + 1 - PRIV_CAP > 0 ? WW + 1 - PRIV_CAP : 0;
@@ -43,7 +44,7 @@ __global__ void __maxnreg__(CG_V3_MAXNREG)
 #else
 __global__ void __launch_bounds__(WARPS3 * 32, CG_V3_MINB)
 #endif
-count_kernel_v3(const CountParams P) {
+count_kernel_v3(const __grid_constant__ CountParams P) {
     using C2 = V2Cfg<KK, WW>;
     using C = V3Cfg<KK, WW, SMALL>;
     constexpr int NW = ModeTraits<MODE>::NW;
@@ -82,13 +83,22 @@ count_kernel_v3(const CountParams P) {
         if (lane == 0) t = atomicAdd(P.work_counter, 1u);
         return __shfl_sync(0xFFFFFFFFu, t, 0);
     };
-    // prefetched vectors of the next tile, tagged by their (16-byte aligned) global address
-    const uint8_t *pf_addr = nullptr;
+    // prefetched vectors of the next tile, tagged by the batch index of the tile's first base (+1; 0 = nothing staged).
+    // ASCII transport: 16 bases per vector, aligned in global memory; packed transport: 32 rank nibbles per vector.
+    // (P is also passed by reference to out-of-line helpers, so it has a local-memory copy: the lambdas below must capture plain
+    // values, not P, or every use turns into a local load inside the hot loop)
+    const bool packed = P.packed != 0;
+    const uint8_t *const gbases = P.bases;
+    uint64_t pf_tag = 0;
     const uint32_t raw_s = uint32_t(__cvta_generic_to_shared(raw));
-    auto prefetch = [&](const uint8_t *gsrc, uint32_t nb) {
-        const uint32_t head = uint32_t(reinterpret_cast<uintptr_t>(gsrc) & 15u);
-        const uint4 *vsrc = reinterpret_cast<const uint4 *>(gsrc - head);
-        const uint32_t nvec = (head + nb + 15u) >> 4;
+    auto tile_head = [&](uint64_t G) -> uint32_t {
+        return packed ? uint32_t(G & 31u) : uint32_t(reinterpret_cast<uintptr_t>(gbases + G) & 15u);
+    };
+    auto tile_nvec = [&](uint32_t head, uint32_t nb) -> uint32_t { return packed ? (head + nb + 31u) >> 5 : (head + nb + 15u) >> 4; };
+    auto prefetch = [&](uint64_t G, uint32_t nb) {
+        const uint32_t head = tile_head(G);
+        const uint4 *vsrc = packed ? reinterpret_cast<const uint4 *>(gbases) + (G >> 5) : reinterpret_cast<const uint4 *>(gbases + G - head);
+        const uint32_t nvec = tile_nvec(head, nb);
 #pragma unroll
         for (int q = 0; q < C::NVL; ++q) {
             const uint32_t i = lane + q * 32;
@@ -96,7 +106,7 @@ count_kernel_v3(const CountParams P) {
                 asm volatile("cp.async.cg.shared.global.L2::cache_hint [%0], [%1], 16, %2;" ::"r"(raw_s + 16u * i), "l"(vsrc + i), "l"(pol_stream) : "memory");
         }
         asm volatile("cp.async.commit_group;" ::: "memory");
-        pf_addr = gsrc;
+        pf_tag = G + 1;
     };
 
     Tally<MODE> T;
@@ -107,8 +117,8 @@ count_kernel_v3(const CountParams P) {
         const uint32_t seg0 = P.read_seg ? P.read_seg[r] : r;
         const uint32_t seg1 = P.read_seg ? P.read_seg[r + 1] : r + 1;
         // address of the first tile of the next read (prefetch target while this read's last tile is processed)
-        const uint8_t *next_read_src = nullptr;
-        uint32_t next_read_nb = 0;
+        uint64_t next_read_G = 0;
+        uint32_t next_read_nb = 0;   // 0: no prediction
         if (nxt < P.n_reads) {
             const uint32_t ns = P.read_seg ? P.read_seg[nxt] : nxt;
             const uint64_t nbase = P.seg_off[ns];
@@ -116,7 +126,7 @@ count_kernel_v3(const CountParams P) {
             if (nlen >= uint64_t(KK + WW - 1)) {
                 const uint64_t nwin = nlen - KK + 1 - WW + 1;
                 const uint32_t tw = uint32_t(nwin < uint64_t(C::TW) ? nwin : uint64_t(C::TW));
-                next_read_src = P.bases + nbase;
+                next_read_G = nbase;
                 next_read_nb = tw + WW - 1 + KK - 1;
             }
         }
@@ -173,13 +183,13 @@ count_kernel_v3(const CountParams P) {
                     uint64_t best = VMAX;
                     for (uint32_t i = lane; i < nkm; i += 32) {
                         uint64_t f = 0, rc = 0;
-                        for (int j = 0; j < KK; ++j) f = f * 5u + (S.lut[P.bases[sbase + i + j]] & 15u);
-                        for (int j = KK; j-- > 0;) rc = rc * 5u + (S.lut[P.bases[sbase + i + j]] >> 4);
+                        for (int j = 0; j < KK; ++j) f = f * 5u + (code_at(gbases, packed, S.lut, sbase + i + j) & 15u);
+                        for (int j = KK; j-- > 0;) rc = rc * 5u + (code_at(gbases, packed, S.lut, sbase + i + j) >> 4);
                         best = umin64(best, umin64(f ^ seed, rc ^ seed));
                     }
 #pragma unroll
                     for (int o = 16; o > 0; o >>= 1) best = umin64(best, __shfl_xor_sync(0xFFFFFFFFu, best, o));
-                    if (lane == 0) process_exact<MODE>(P, S, s_nhash, best, do_tot, do_unq);
+                    if (lane == 0) { const Smem2 Sx = S; process_exact<MODE>(P, Sx, s_nhash, best, do_tot, do_unq); }   // a copy: S itself must never have its address taken
                     __syncwarp();
                     continue;
                 }
@@ -192,21 +202,30 @@ count_kernel_v3(const CountParams P) {
                     const uint32_t nb = nk + KK - 1;
                     const bool last_tile = (g0 + Tw >= nwin);
                     // ---- phase 0: (prefetched) 16-byte vectors -> code bytes in shared memory -----------------------
-                    const uint8_t *gsrc = P.bases + sbase + g0;
-                    const uint32_t head = uint32_t(reinterpret_cast<uintptr_t>(gsrc) & 15u);
-                    const uint32_t nvec = (head + nb + 15u) >> 4;
-                    if (pf_addr != gsrc) prefetch(gsrc, nb);          // not predicted: load now
+                    const uint64_t G = sbase + g0;
+                    const uint32_t head = tile_head(G);
+                    const uint32_t nvec = tile_nvec(head, nb);
+                    if (pf_tag != G + 1) prefetch(G, nb);             // not predicted: load now
                     asm volatile("cp.async.wait_all;" ::: "memory");
                     __syncwarp();                                      // staging complete for every lane; previous tile's readers of codes are done
+                    if (packed) {
+                        if (lane < nvec) {   // a tile is at most 26 vectors of 32 bases
+                            uint4 a, b;
+                            decode_packed16(raw[lane], a, b);
+                            *reinterpret_cast<uint4 *>(S.codes + 32 + 32 * lane) = a;
+                            *reinterpret_cast<uint4 *>(S.codes + 32 + 32 * lane + 16) = b;
+                        }
+                    } else {
 #pragma unroll
-                    for (int q = 0; q < C::NVL; ++q) {
-                        const uint32_t i = lane + q * 32;
-                        if (i < nvec) {
-                            const uint4 x = raw[i];
-                            uint4 y;
-                            y.x = encode4(S.lut, x.x); y.y = encode4(S.lut, x.y);
-                            y.z = encode4(S.lut, x.z); y.w = encode4(S.lut, x.w);
-                            *reinterpret_cast<uint4 *>(S.codes + 32 + 16 * i) = y;
+                        for (int q = 0; q < C::NVL; ++q) {
+                            const uint32_t i = lane + q * 32;
+                            if (i < nvec) {
+                                const uint4 x = raw[i];
+                                uint4 y;
+                                y.x = encode4(S.lut, x.x); y.y = encode4(S.lut, x.y);
+                                y.z = encode4(S.lut, x.z); y.w = encode4(S.lut, x.w);
+                                *reinterpret_cast<uint4 *>(S.codes + 32 + 16 * i) = y;
+                            }
                         }
                     }
                     __syncwarp();   // every lane has consumed its staged vectors: the buffer may be refilled
@@ -214,10 +233,10 @@ count_kernel_v3(const CountParams P) {
                     if (!last_tile) {
                         const uint64_t g1 = g0 + Tw - 1;
                         const uint32_t tw1 = uint32_t(nwin - g1 < uint64_t(C::TW) ? nwin - g1 : uint64_t(C::TW));
-                        prefetch(P.bases + sbase + g1, tw1 + WW - 1 + KK - 1);
-                    } else if (last_pass && seg + 1 == seg1 && next_read_src) {
-                        prefetch(next_read_src, next_read_nb);
-                    } else pf_addr = nullptr;
+                        prefetch(sbase + g1, tw1 + WW - 1 + KK - 1);
+                    } else if (last_pass && seg + 1 == seg1 && next_read_nb) {
+                        prefetch(next_read_G, next_read_nb);
+                    } else pf_tag = 0;
                     __syncwarp();
                     // ---- phase 1: rolling canonical hash of the lane's block, prefix minima -> smem -------------------
                     const uint32_t k0 = lane * WW;
@@ -308,7 +327,7 @@ count_kernel_v3(const CountParams P) {
                         __syncwarp();
                         if (lane == 0) *s_carry_valid = 0;   // re-armed by the walker of the run alive at the last window
                         __syncwarp();
-                        exact_tile<MODE, WW>(P, S, s_nhash, s_carry_pos, s_carry_valid, Tw, first, carry, g0, do_tot, do_unq, lane, 32u);
+                        { const Smem2 Sx = S; exact_tile<MODE, WW>(P, Sx, s_nhash, s_carry_pos, s_carry_valid, Tw, first, carry, g0, do_tot, do_unq, lane, 32u); }
                         nl = 0;
                     }
                     __syncwarp();

@@ -76,6 +76,7 @@ public:
                 std::fprintf(stderr, "charon: GPU %d: %s\n", g, m.c_str());
                 return 1;
             }
+            cg_set_host_pack(s->h, -1, std::max(1, int(opt_.threads)));   // -t also sizes the library's packing pool
             gpu_.push_back(std::move(s));
         }
         if (opt_.partition_filter && opt_.gpus > 1)

@@ -209,6 +209,16 @@ int cg_run_staged(cg_handle *h, int with_eval);                                 
 int cg_fetch_staged(cg_handle *h, const cg_counts_out *counts_out, const cg_calls_out *calls_out); /* D2H + sync */
 
 /* ---- pinned host memory + device-side timing (CUDA events on the handle's stream) ---------- */
+/* Transport of the bases.  The batch a caller hands over is ASCII, one base per byte (what the reference's parser yields,
+ * src/dehost_main.cpp:335-339); at 8 kb per read that makes PCIe the end-to-end bound.  When the k=19 / w=41 kernels
+ * apply, the library can pack the bases to 4-bit dna5 ranks on a host thread pool, chunk by chunk, and copy the packed
+ * chunks while the next ones are being packed; the kernels expand a nibble to the very code they derive from ASCII.
+ * mode: -1 automatic (pool of >= 8 threads), 0 never, 1 always.  threads > 0 resizes the process-wide pool
+ * (default: env CHARON_HOST_THREADS, else min(16, hardware threads)).  Env CHARON_HOST_PACK presets the mode of new handles. */
+int cg_set_host_pack(cg_handle *h, int mode, int threads);
+/* packed[i >> 1] nibble (i & 1) = dna5 rank of bases[i] (A0 C1 G2 N3 T4; U -> T, anything else -> N); (n + 1) / 2 bytes. Host only. */
+int cg_pack_bases(const char *bases, uint64_t n, uint8_t *packed);
+
 int cg_host_alloc(size_t bytes, void **out);   /* cudaHostAlloc: pinned buffers for cg_batch / outputs */
 void cg_host_free(void *p);
 /* Everything enqueued on the handle between start and stop is timed with one event pair; additionally every
@@ -235,6 +245,9 @@ typedef struct cg_info {
     float last_count_kernel_ms;   /* CUDA-event time of the count kernel of the last batch */
     float last_eval_kernel_ms;
     float last_h2d_ms, last_d2h_ms;
+    uint64_t last_h2d_bytes;      /* bytes the last staged batch moved host -> device (bases as sent + offsets + scalars) */
+    float last_pack_ms;           /* host wall time of the 4-bit packing (its chunk copies overlap it) */
+    uint32_t last_packed;         /* 1 when the last batch went over the link as 4-bit ranks */
 } cg_info;
 int cg_get_info(cg_handle *h, cg_info *out);
 
