@@ -170,6 +170,7 @@ cgk::CountParams make_params(cg_handle *h) {
     P.long_read_min = 0; P.long_only = 0;
     P.dbg_out = nullptr; P.dbg_cap = 0; P.dbg_n = nullptr;
     P.n_parts = h->n_parts; P.my_part = h->my_part; P.rows_per_part = h->rows_per_part; P.packed = h->staged_packed ? 1 : 0;
+    P.part_pad = 0;
     for (int i = 0; i < CG_MAX_PARTS; ++i) P.part_base[i] = h->part_base[i];
     return P;
 }

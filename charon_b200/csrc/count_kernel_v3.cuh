@@ -18,7 +18,7 @@ namespace cgk {
 #define CG_V3_MINB 3
 #endif
 constexpr int WARPS3 = CG_V3_WARPS;    // warps per CTA (independent of each other)
-constexpr int WLIST_CAP = 256;         // compacted emission list of a warp tile (expected ~65 entries)
+constexpr int WLIST_CAP = 256;         // emission ring of a warp (power of two; a tile emits ~60 entries, up to two tiles' worth wait in it)
 
 template <int KK, int WW, bool SMALL> struct V3Cfg {
     static constexpr int NK = 32 * WW;            // k-mers per warp tile
@@ -151,7 +151,13 @@ count_kernel_v3(const __grid_constant__ CountParams P) {
             for (int j = 0; j < NW; ++j) bm[j] = S.bestmask[j];
             const bool last_pass = (pass == npass - 1);
 
-            uint32_t pend = 0;   // emitted values waiting at the front of S.list for a full group of 32 (warp-uniform)
+            // S.list is a ring: `pend` emitted values starting at `qh` wait to be queried (warp-uniform); only full groups of 32 are
+            // queried per tile, the rest waits for the next tile's emissions.
+            // (Measured and dropped: pulling the rows into L2 one tile ahead with prefetch.global.L2 made the human-scale launch
+            // 50 % slower; fetching them with 4-byte cp.async into shared memory 15 % slower.)
+            uint32_t pend = 0, qh = 0;
+            uint64_t *const ring = S.list;
+            auto LI = [&](uint32_t x) -> uint64_t & { return ring[(qh + x) & uint32_t(WLIST_CAP - 1)]; };
             // Deferred gathers (narrow rows, 3 hash functions, local filter): the row loads of up to DQ groups are issued at the
             // end of a tile and consumed after the NEXT tile's hashing, so the HBM / L2 latency hides behind arithmetic.
             constexpr int DQ = (MODE == 0) ? 3 : 0;
@@ -314,7 +320,7 @@ count_kernel_v3(const __grid_constant__ CountParams P) {
                     const bool redo = __any_sync(0xFFFFFFFFu, tie) || pend + nl > WLIST_CAP;
                     if (!redo) {
                         uint32_t dst = pend + inc - cnt;
-                        for (uint32_t q = 0; q < cnt; ++q, ++dst) S.list[dst] = pslot0[q];
+                        for (uint32_t q = 0; q < cnt; ++q, ++dst) LI(dst) = pslot0[q];
                         if (lane == 0) *s_carry_valid = 0;
                     } else {
                         // ---- exact path: raw values to smem, per-run chain walk, inline emission ------------------------
@@ -336,20 +342,20 @@ count_kernel_v3(const __grid_constant__ CountParams P) {
                         unsigned long long base = 0;
                         if (lane == 0) base = atomicAdd(P.dbg_n, (unsigned long long)nl);
                         base = __shfl_sync(0xFFFFFFFFu, base, 0);
-                        for (uint32_t i = lane; i < nl; i += 32) if (base + i < P.dbg_cap) P.dbg_out[base + i] = S.list[pend + i];
+                        for (uint32_t i = lane; i < nl; i += 32) if (base + i < P.dbg_cap) P.dbg_out[base + i] = LI(pend + i);
                     }
                     if (lane == 0 && do_tot && nl) atomicAdd(s_nhash, nl);
                     if (P.filter) {
                         // only full groups of 32 are queried now; the remainder waits for the next tile's emissions
-                        const uint32_t have = pend + nl, fullg = have & ~31u;
+                        const uint32_t fullg = (pend + nl) & ~31u;
                         uint32_t first_now = 0;   // groups below this index go through the deferred queue
                         if (can_defer) {
-                            dq_finish();          // loads issued one tile ago: their latency is behind us
+                            dq_finish();          // loads issued one tile ago
                             const uint32_t ngroups = fullg >> 5;
 #pragma unroll
                             for (int g = 0; g < DQ; ++g)
                                 if (uint32_t(g) < ngroups) {
-                                    const uint64_t value = S.list[g * 32 + lane];
+                                    const uint64_t value = LI(g * 32 + lane);
                                     uint32_t sh = 0;
 #pragma unroll
                                     for (int i = 0; i < 3; ++i) {
@@ -363,17 +369,11 @@ count_kernel_v3(const __grid_constant__ CountParams P) {
                             first_now = ndq * 32;
                         }
                         for (uint32_t i = first_now + lane; i < fullg; i += 32) {
-                            const Mask<NW> m = bulk_contains<MODE>(P, S.list[i], pol_filter);
+                            const Mask<NW> m = bulk_contains<MODE>(P, LI(i), pol_filter);
                             T.add(m, bm, small_bins, do_tot, do_unq, S);
                         }
-                        const uint32_t rem = have - fullg;
-                        if (fullg) {
-                            uint64_t x = 0;
-                            if (lane < rem) x = S.list[fullg + lane];
-                            __syncwarp();
-                            if (lane < rem) S.list[lane] = x;
-                        }
-                        pend = rem;
+                        qh = (qh + fullg) & uint32_t(WLIST_CAP - 1);
+                        pend = pend + nl - fullg;
                     }
                     if (last_tile) break;
                     g0 += Tw - 1;
@@ -381,10 +381,10 @@ count_kernel_v3(const __grid_constant__ CountParams P) {
                 }  // tiles
             }      // segments
             dq_finish();
-            if (pend) {   // flush the last partial group of this pass
+            if (pend) {   // flush what is still waiting at the end of this pass
                 __syncwarp();
-                if (lane < pend) {
-                    const Mask<NW> m = bulk_contains<MODE>(P, S.list[lane], pol_filter);
+                for (uint32_t i = lane; i < pend; i += 32) {
+                    const Mask<NW> m = bulk_contains<MODE>(P, LI(i), pol_filter);
                     T.add(m, bm, small_bins, do_tot, do_unq, S);
                 }
                 pend = 0;

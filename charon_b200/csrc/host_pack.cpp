@@ -1,5 +1,5 @@
-// charon_b200/csrc/host_pack.cpp — ASCII -> 4-bit rank packing on host threads (see host_pack.hpp).  Plain C++17 + AVX2
-// intrinsics behind a run-time CPU check; compiled by the host compiler and linked into libcharon_gpu.so.
+// charon_b200/csrc/host_pack.cpp — ASCII -> 4-bit rank packing on host threads (see host_pack.hpp).  Plain C++17 + AVX2 /
+// AVX-512BW intrinsics behind a run-time CPU check; compiled by the host compiler and linked into libcharon_gpu.so.
 #include "host_pack.hpp"
 
 #include <algorithm>
@@ -56,7 +56,44 @@ __attribute__((target("avx2"))) void pack_avx2(const uint8_t *src, uint8_t *dst,
     }
     if (i < end) pack_scalar(src, dst, i, end);
 }
+
+// Same algorithm on 512-bit registers: 128 characters -> 64 bytes per iteration.
+__attribute__((target("avx512f,avx512bw"))) void pack_avx512(const uint8_t *src, uint8_t *dst, uint64_t begin, uint64_t end) {
+    const __m512i lo_tbl = _mm512_broadcast_i32x4(_mm_setr_epi8(0, 1, 0, 2, 8, 8, 0, 4, 0, 0, 0, 0, 0, 0, 0, 0));
+    const __m512i hi_tbl = _mm512_broadcast_i32x4(_mm_setr_epi8(0, 0, 0, 0, 7, 8, 7, 8, 0, 0, 0, 0, 0, 0, 0, 0));
+    const __m512i rk_tbl = _mm512_broadcast_i32x4(_mm_setr_epi8(3, 0, 1, 3, 2, 3, 3, 3, 4, 3, 3, 3, 3, 3, 3, 3));
+    const __m512i nib = _mm512_set1_epi8(0x0F), mul = _mm512_set1_epi16(0x1001);
+    const __m512i order = _mm512_setr_epi64(0, 2, 4, 6, 1, 3, 5, 7);   // packus interleaves the two sources per 128-bit lane
+    auto ranks = [&](const uint8_t *p) __attribute__((target("avx512f,avx512bw"))) {
+        const __m512i c = _mm512_loadu_si512(reinterpret_cast<const void *>(p));
+        const __m512i lo = _mm512_shuffle_epi8(lo_tbl, _mm512_and_si512(c, nib));
+        const __m512i hi = _mm512_shuffle_epi8(hi_tbl, _mm512_and_si512(_mm512_srli_epi16(c, 4), nib));
+        return _mm512_maddubs_epi16(_mm512_shuffle_epi8(rk_tbl, _mm512_and_si512(lo, hi)), mul);
+    };
+    uint64_t i = begin;
+    if ((reinterpret_cast<uintptr_t>(dst + (i >> 1)) & 63u) == 0) {
+        for (; i + 128 <= end; i += 128) {
+            const __m512i q = _mm512_permutexvar_epi64(order, _mm512_packus_epi16(ranks(src + i), ranks(src + i + 64)));
+            _mm512_stream_si512(reinterpret_cast<__m512i *>(dst + (i >> 1)), q);
+        }
+        _mm_sfence();
+    }
+    for (; i + 128 <= end; i += 128) {
+        const __m512i q = _mm512_permutexvar_epi64(order, _mm512_packus_epi16(ranks(src + i), ranks(src + i + 64)));
+        _mm512_storeu_si512(reinterpret_cast<void *>(dst + (i >> 1)), q);
+    }
+    if (i < end) pack_avx2(src, dst, i, end);
+}
 #endif
+
+bool have_avx512() {
+#if defined(__x86_64__)
+    static const bool v = __builtin_cpu_supports("avx512f") && __builtin_cpu_supports("avx512bw") && !std::getenv("CHARON_NO_AVX512");
+    return v;
+#else
+    return false;
+#endif
+}
 
 bool have_avx2() {
 #if defined(__x86_64__)
@@ -141,6 +178,7 @@ int resolve_threads() {
 
 void pack_range(const uint8_t *src, uint8_t *dst, uint64_t begin, uint64_t end) {
 #if defined(__x86_64__)
+    if (have_avx512()) { pack_avx512(src, dst, begin, end); return; }
     if (have_avx2()) { pack_avx2(src, dst, begin, end); return; }
 #endif
     pack_scalar(src, dst, begin, end);
