@@ -12,6 +12,8 @@
 #include <math_constants.h>
 #include <stdint.h>
 
+#include "kde_exp_table.inc"
+
 namespace cgk {
 
 struct ModelDev {            // one per category, device-resident
@@ -41,14 +43,24 @@ struct EvalParams {
     double *prob; uint8_t *call; uint8_t *confidence;
 };
 
+// One KDE term: float(exp(-z^2 / 2) / sqrt(2 pi)) exactly as the reference rounds it, without libm's exp and without the
+// double division (kde_fast_exp.inc; proven identical on every float of [-15, 15] by tests/kde_exp_exhaustive.c).
+__constant__ double c_exp_t64[64] = CG_EXP_T64_INIT;
+#define CG_KDE_FN __device__ __forceinline__
+#define CG_KDE_TPARAM , const double *__restrict__ cg_t64
+#define CG_KDE_TABLE(j) cg_t64[j]
+#define CG_KDE_MUL(a, b) __dmul_rn(a, b)
+#define CG_KDE_BITS(d) ((unsigned long long)__double_as_longlong(d))
+#define CG_KDE_FROM_BITS(b) __longlong_as_double((long long)(b))
+#include "kde_fast_exp.inc"
+
 __device__ __forceinline__ float kde_z(const float *__restrict__ ds, uint32_t i, float h, float x) { return __fdiv_rn(__fsub_rn(x, ds[i]), h); }
 
 // `sorted`: ds ascending, so z_i = (x - ds[i]) / h is non-increasing in i (IEEE subtraction and division by h > 0 are monotone)
 // and the terms that survive the |z| <= 15 test form one contiguous range, found by two binary searches with the very same
 // float expression; everything outside contributes exactly +0.0f.  The range is then summed in dataset order as before.
-__device__ __forceinline__ float kde_prob(const float *__restrict__ ds, uint32_t n, float h, float x, bool sorted) {
+__device__ __forceinline__ float kde_prob(const float *__restrict__ ds, uint32_t n, float h, float x, bool sorted, const double *__restrict__ t64) {
     float total = 0.0f;
-    const double inv_sqrt = 2.5066282746310002;  // sqrt(2 * 3.141592653589793238463) in double
     uint32_t i0 = 0, i1 = n;
     if (sorted && !isnan(x) && h > 0.0f) {
         uint32_t lo = 0, hi = n;                 // first i with z_i <= 15
@@ -60,9 +72,8 @@ __device__ __forceinline__ float kde_prob(const float *__restrict__ ds, uint32_t
     for (uint32_t i = i0; i < i1; ++i) {
         const float z = kde_z(ds, i, h, x);
         if (fabsf(z) > 15.0f) continue;                                 // term rounds to exactly +0.0f
-        const double zz = double(z) * double(z);                         // std::pow(float,2) -> exact in double
-        const float kf = float(exp(-zz / 2.0) / inv_sqrt);
-        total = __fadd_rn(total, kf);
+        if (z != z) { total = __fadd_rn(total, z); continue; }           // exp(NaN) = NaN poisons the sum, as in the reference
+        total = __fadd_rn(total, kde_term(z, t64));
     }
     return __fdiv_rn(total, __fmul_rn(h, float(n)));                    // NaN z falls through: exp(NaN) = NaN
 }
@@ -91,6 +102,9 @@ __device__ __forceinline__ float dgamma_dev(float x, float shape, float scale) {
 
 // one thread per (read, category): probabilities_[i] = 1.0 * Model::prob(unique_proportions_[i]).pos
 __global__ void prob_kernel(const EvalParams P) {
+    __shared__ double s_t64[64];   // 2^(j/64): per-lane indices differ, so shared memory, not the constant cache
+    if (threadIdx.x < 64) s_t64[threadIdx.x] = c_exp_t64[threadIdx.x];
+    __syncthreads();
     const size_t idx = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
     if (idx >= size_t(P.n_reads) * P.ncat) return;
     const uint32_t r = uint32_t(idx / P.ncat), c = uint32_t(idx % P.ncat);
@@ -99,8 +113,8 @@ __global__ void prob_kernel(const EvalParams P) {
     const float p_err = dexp300(x, P.log_rate);
     float p_pos, p_neg;
     if (m.dist == 0) {
-        p_pos = kde_prob(P.pool + m.pos_off, m.npos, m.h_pos, x, m.pos_sorted != 0);
-        p_neg = kde_prob(P.pool + m.neg_off, m.nneg, m.h_neg, x, m.neg_sorted != 0);
+        p_pos = kde_prob(P.pool + m.pos_off, m.npos, m.h_pos, x, m.pos_sorted != 0, s_t64);
+        p_neg = kde_prob(P.pool + m.neg_off, m.nneg, m.h_neg, x, m.neg_sorted != 0, s_t64);
     } else if (m.dist == 2) {
         p_pos = dgamma_dev(__fsub_rn(x, m.gamma_pos[1]), m.gamma_pos[0], m.gamma_pos[2]);
         p_neg = dgamma_dev(__fsub_rn(x, m.gamma_neg[1]), m.gamma_neg[0], m.gamma_neg[2]);
