@@ -19,10 +19,20 @@ namespace cgh {
 
 namespace {
 
+#ifndef PACK_NT_DEFAULT
+#define PACK_NT_DEFAULT true
+#endif
+
 void pack_scalar(const uint8_t *src, uint8_t *dst, uint64_t begin, uint64_t end) {
     uint64_t i = begin;
     for (; i + 1 < end; i += 2) dst[i >> 1] = uint8_t(rank_of(src[i]) | (rank_of(src[i + 1]) << 4));
     if (i < end) dst[i >> 1] = rank_of(src[i]);
+}
+
+// Streaming (non-temporal) stores for the packed buffer: CHARON_PACK_NT=1/0.
+bool use_nt_stores() {
+    static const bool v = [] { const char *e = std::getenv("CHARON_PACK_NT"); return e ? std::atoi(e) != 0 : PACK_NT_DEFAULT; }();
+    return v;
 }
 
 #if defined(__x86_64__)
@@ -43,7 +53,7 @@ __attribute__((target("avx2"))) void pack_avx2(const uint8_t *src, uint8_t *dst,
     };
     uint64_t i = begin;
     // the packed buffer is written once and next read by the copy engine: streaming stores when the alignment allows
-    if ((reinterpret_cast<uintptr_t>(dst + (i >> 1)) & 31u) == 0) {
+    if (use_nt_stores() && (reinterpret_cast<uintptr_t>(dst + (i >> 1)) & 31u) == 0) {
         for (; i + 64 <= end; i += 64) {
             const __m256i q = _mm256_permute4x64_epi64(_mm256_packus_epi16(ranks(src + i), ranks(src + i + 32)), 0xD8);
             _mm256_stream_si256(reinterpret_cast<__m256i *>(dst + (i >> 1)), q);
@@ -71,7 +81,7 @@ __attribute__((target("avx512f,avx512bw"))) void pack_avx512(const uint8_t *src,
         return _mm512_maddubs_epi16(_mm512_shuffle_epi8(rk_tbl, _mm512_and_si512(lo, hi)), mul);
     };
     uint64_t i = begin;
-    if ((reinterpret_cast<uintptr_t>(dst + (i >> 1)) & 63u) == 0) {
+    if (use_nt_stores() && (reinterpret_cast<uintptr_t>(dst + (i >> 1)) & 63u) == 0) {
         for (; i + 128 <= end; i += 128) {
             const __m512i q = _mm512_permutexvar_epi64(order, _mm512_packus_epi16(ranks(src + i), ranks(src + i + 64)));
             _mm512_stream_si512(reinterpret_cast<__m512i *>(dst + (i >> 1)), q);
