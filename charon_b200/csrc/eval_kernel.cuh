@@ -50,6 +50,7 @@ __constant__ double c_exp_t64[64] = CG_EXP_T64_INIT;
 #define CG_KDE_TPARAM , const double *__restrict__ cg_t64
 #define CG_KDE_TABLE(j) cg_t64[j]
 #define CG_KDE_MUL(a, b) __dmul_rn(a, b)
+#define CG_KDE_ADD(a, b) __dadd_rn(a, b)
 #define CG_KDE_BITS(d) ((unsigned long long)__double_as_longlong(d))
 #define CG_KDE_FROM_BITS(b) __longlong_as_double((long long)(b))
 #include "kde_fast_exp.inc"

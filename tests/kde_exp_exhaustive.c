@@ -10,10 +10,12 @@ static const double T64[64] = CG_EXP_T64_INIT;
 static inline uint64_t bits_of(double d) { uint64_t b; memcpy(&b, &d, 8); return b; }
 static inline double from_bits(uint64_t b) { double d; memcpy(&d, &b, 8); return d; }
 static inline double mul_rn(double a, double b) { volatile double x = a * b; return x; }
+static inline double add_rn(double a, double b) { volatile double x = a + b; return x; }
 #define CG_KDE_FN static inline
 #define CG_KDE_TPARAM
 #define CG_KDE_TABLE(j) T64[j]
 #define CG_KDE_MUL(a, b) mul_rn(a, b)
+#define CG_KDE_ADD(a, b) add_rn(a, b)
 #define CG_KDE_BITS(d) bits_of(d)
 #define CG_KDE_FROM_BITS(b) from_bits(b)
 #include "../charon_b200/csrc/kde_fast_exp.inc"
