@@ -110,11 +110,18 @@ __device__ __forceinline__ Mask<(MODE == 2 ? 2 : (MODE == 3 ? 4 : 1))> fetch_row
 }
 
 // seqan3 interleaved_bloom_filter::hash_and_fit without the final * technical_bins
-__device__ __forceinline__ uint64_t ibf_row(uint64_t h, uint64_t seed, uint32_t hash_shift, uint64_t bin_size) {
+// bin_size < 2^32 always (include/index_arguments.hpp:20 caps it at 2^32 - 3; cg_create / cg_build_index reject more), so
+// floor(h * bin_size / 2^64) needs two 32 x 32 -> 64 products instead of a full 64 x 64 high product, and a row is 32 bits.
+__device__ __forceinline__ uint32_t ibf_row32(uint64_t h, uint64_t seed, uint32_t hash_shift, uint32_t bin_size) {
     h *= seed;
     h ^= h >> hash_shift;
     h *= 11400714819323198485ULL;
-    return __umul64hi(h, bin_size);
+    const uint64_t t = uint64_t(uint32_t(h)) * bin_size;
+    const uint64_t u = uint64_t(uint32_t(h >> 32)) * bin_size + (t >> 32);   // <= (2^32-1)^2 + 2^32 - 1 < 2^64
+    return uint32_t(u >> 32);
+}
+__device__ __forceinline__ uint64_t ibf_row(uint64_t h, uint64_t seed, uint32_t hash_shift, uint64_t bin_size) {
+    return ibf_row32(h, seed, hash_shift, uint32_t(bin_size));
 }
 
 // MODE 0: row width <= 32 bits (runtime 1<<row_shift), MODE 1: 64, MODE 2: 128, MODE 3: 256
@@ -128,11 +135,11 @@ template <int MODE>
 __device__ __forceinline__ Mask<ModeTraits<MODE>::NW> fetch_row(const void *filter, uint64_t row, uint32_t row_shift, uint64_t pol) {
     Mask<ModeTraits<MODE>::NW> m;
     if (MODE == 0) {
-        uint64_t bit = row << row_shift;
-        uint32_t word = ldg_na_u32(reinterpret_cast<const uint32_t *>(filter) + (bit >> 5), pol);
+        const uint32_t r = uint32_t(row);   // 32-bit arithmetic: word index = (r << row_shift) >> 5 without forming the 64-bit bit index
+        uint32_t word = ldg_na_u32(reinterpret_cast<const uint32_t *>(filter) + (r >> (5u - row_shift)), pol);
         uint32_t rb = 1u << row_shift;
         uint32_t msk = rb >= 32 ? 0xFFFFFFFFu : ((1u << rb) - 1u);
-        m.w[0] = (word >> (uint32_t(bit) & 31u)) & msk;
+        m.w[0] = (word >> ((r << row_shift) & 31u)) & msk;
     } else if (MODE == 1) {
         m.w[0] = ldg_na_u64(reinterpret_cast<const uint64_t *>(filter) + row, pol);
     } else if (MODE == 2) {

@@ -359,9 +359,9 @@ count_kernel_v3(const __grid_constant__ CountParams P) {
                                     uint32_t sh = 0;
 #pragma unroll
                                     for (int i = 0; i < 3; ++i) {
-                                        const uint64_t bit = ibf_row(value, c_ibf_seeds[i], P.hash_shift, P.bin_size) << P.row_shift;
-                                        dq_w[g][i] = ldg_na_u32(reinterpret_cast<const uint32_t *>(P.filter) + (bit >> 5), pol_filter);
-                                        sh |= (uint32_t(bit) & 31u) << (5 * i);
+                                        const uint32_t row = ibf_row32(value, c_ibf_seeds[i], P.hash_shift, uint32_t(P.bin_size));
+                                        dq_w[g][i] = ldg_na_u32(reinterpret_cast<const uint32_t *>(P.filter) + (row >> (5u - P.row_shift)), pol_filter);
+                                        sh |= ((row << P.row_shift) & 31u) << (5 * i);
                                     }
                                     dq_sh[g] = sh;
                                 }
