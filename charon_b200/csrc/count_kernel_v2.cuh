@@ -79,6 +79,9 @@ __device__ __forceinline__ uint32_t encode4(const uint8_t *lut, uint32_t w) {   
            (uint32_t(lut[w >> 24]) << 24);
 }
 __device__ __forceinline__ uint64_t umin64(uint64_t a, uint64_t b) { return a < b ? a : b; }
+// Store through a 32-bit shared-space address.  A moving generic pointer costs a 64-bit add next to the address the STS uses;
+// deliberately no "memory" clobber (the window-minimum loads around it must stay free to move): the caller fences once.
+__device__ __forceinline__ void st_shared_u64(uint32_t addr, uint64_t v) { asm volatile("st.shared.u64 [%0], %1;" ::"r"(addr), "l"(v)); }
 
 // Packed transport (host_pack.hpp): a nibble is the dna5 rank.  PRMT with the nibbles themselves as byte selectors expands
 // four bases per instruction into exactly the code bytes base_code() yields for ASCII (rank | complement rank << 4).
@@ -150,7 +153,7 @@ __device__ __forceinline__ void scan_window(const uint64_t *arr, uint32_t w, uin
 // just values) would matter: equal low words between the two operands of any min, or between the value that has just
 // left the window and the new minimum (an equal value exactly W k-mers apart).
 template <int WW, bool EDGE>
-__device__ __forceinline__ void p2_block(uint64_t (&v)[WW], uint64_t vleft, const uint64_t *next, uint32_t k0, uint32_t Tw, uint64_t *&pslot,
+__device__ __forceinline__ void p2_block(uint64_t (&v)[WW], uint64_t vleft, const uint64_t *next, uint32_t k0, uint32_t Tw, uint32_t &pa,
                                          bool &tie) {
     uint64_t sv = v[WW - 1], mw_next = 0;
 #pragma unroll
@@ -169,7 +172,7 @@ __device__ __forceinline__ void p2_block(uint64_t (&v)[WW], uint64_t vleft, cons
             // low words suffice: two DIFFERENT adjacent window minima with equal low words always trip one of the tie flags
             // (old minimum left: `leaving` check; newcomer took over: it met the old minimum in a prefix / suffix / combine step)
             const bool start = (lo32(mw_next) != lo32(mw)) & (!EDGE || (k0 + j + 1 < Tw));
-            if (start) { *pslot = mw_next; ++pslot; }
+            if (start) { st_shared_u64(pa, mw_next); pa += 8u; }   // one predicated STS + one 32-bit add per window
         }
         mw_next = mw;
     }
@@ -412,17 +415,19 @@ __global__ void __launch_bounds__(NT2, CG_V2_MINB) count_kernel_v2(const __grid_
                     // ---- phase 2: suffix minima + neighbour prefix = window minima; a window whose minimum differs from
                     //      its predecessor's starts a run = one emission, appended to the thread's private slots ----------
                     const uint64_t v0_raw = v[0];
-                    uint64_t *pslot = S.priv + tid * PRIV_CAP;
-                    uint64_t *const pslot0 = pslot;
+                    uint64_t *const pslot0 = S.priv + tid * PRIV_CAP;
+                    const uint32_t pa0 = uint32_t(__cvta_generic_to_shared(pslot0));
+                    uint32_t pa = pa0;   // shared-space address of the next free slot
                     if (active && k0 < Tw) {
                         const bool interior = (k0 + WW <= Tw);   // every window of the block is valid (=> next block's prefix exists)
-                        if (interior) p2_block<WW, false>(v, vleft, S.arr + k0 + WW, k0, Tw, pslot, tie);
-                        else p2_block<WW, true>(v, vleft, S.arr + k0 + WW, k0, Tw, pslot, tie);
+                        if (interior) p2_block<WW, false>(v, vleft, S.arr + k0 + WW, k0, Tw, pa, tie);
+                        else p2_block<WW, true>(v, vleft, S.arr + k0 + WW, k0, Tw, pa, tie);
                         // window k0 against window k0-1 (computed locally in phase 1, no neighbour needed); v[0] now holds min(k0)
-                        if (k0 > 0 ? (v[0] != m_prevwin) : first) { *pslot = v[0]; ++pslot; }
+                        if (k0 > 0 ? (v[0] != m_prevwin) : first) { st_shared_u64(pa, v[0]); pa += 8u; }
                     }
                     {   // compaction: warp scan of the per-thread counts, one shared atomic per warp
-                        const uint32_t cnt = uint32_t(pslot - pslot0);
+                        asm volatile("" ::: "memory");   // the slots were written by st_shared_u64 (no memory clobber of its own): order the reads below
+                    const uint32_t cnt = (pa - pa0) >> 3;
                         tie |= (cnt > PRIV_CAP);            // private slots overrun: redo the tile exactly (results below are discarded)
                         uint32_t inc = cnt;
 #pragma unroll

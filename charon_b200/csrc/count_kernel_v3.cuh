@@ -301,14 +301,16 @@ count_kernel_v3(const __grid_constant__ CountParams P) {
                     __syncwarp();
                     // ---- phase 2: window minima, run starts -> private slots -> warp-compacted list -------------------
                     const uint64_t v0_raw = v[0];
-                    uint64_t *pslot = S.priv + lane * PRIV_CAP;
-                    uint64_t *const pslot0 = pslot;
+                    uint64_t *const pslot0 = S.priv + lane * PRIV_CAP;
+                    const uint32_t pa0 = uint32_t(__cvta_generic_to_shared(pslot0));
+                    uint32_t pa = pa0;   // shared-space address of the next free slot
                     if (active && k0 < Tw) {
-                        if (k0 + WW <= Tw) p2_block<WW, false>(v, vleft, S.arr + k0 + WW, k0, Tw, pslot, tie);
-                        else p2_block<WW, true>(v, vleft, S.arr + k0 + WW, k0, Tw, pslot, tie);
-                        if (k0 > 0 ? (lo32(v[0]) != lo32(m_prevwin)) : first) { *pslot = v[0]; ++pslot; }   // low words: see p2_block
+                        if (k0 + WW <= Tw) p2_block<WW, false>(v, vleft, S.arr + k0 + WW, k0, Tw, pa, tie);
+                        else p2_block<WW, true>(v, vleft, S.arr + k0 + WW, k0, Tw, pa, tie);
+                        if (k0 > 0 ? (lo32(v[0]) != lo32(m_prevwin)) : first) { st_shared_u64(pa, v[0]); pa += 8u; }   // low words: see p2_block
                     }
-                    const uint32_t cnt = uint32_t(pslot - pslot0);
+                    asm volatile("" ::: "memory");   // the slots were written by st_shared_u64 (no memory clobber of its own): order the reads below
+                    const uint32_t cnt = (pa - pa0) >> 3;
                     tie = tie | (cnt > PRIV_CAP);
 #ifdef CG_FORCE_EXACT
                     tie = true;
