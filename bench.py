@@ -104,7 +104,12 @@ def dist_env():
 def cpu_baseline(wl, records, rec_bin, seconds_target=15.0, threads=0):
     """The oracle port (reference loop body restated) on the host cores, bounded sample of the same workload."""
     import oracle
-    threads = threads or oracle.lib().orc_max_threads()
+    # every core this process may run on: torchrun exports OMP_NUM_THREADS=1 to its children, which must not shrink the CPU arm
+    try:
+        host_cores = len(os.sched_getaffinity(0))
+    except AttributeError:
+        host_cores = os.cpu_count() or 1
+    threads = threads or max(host_cores, oracle.lib().orc_max_threads())
     t0 = time.time()
     idx = oracle.Index.build(records, rec_bin, [0, 1], CATEGORIES, threads=threads)
     build_s = time.time() - t0
