@@ -14,6 +14,9 @@ namespace cgk {
 #ifndef CG_V3_WARPS
 #define CG_V3_WARPS 4
 #endif
+#ifndef CG_V3_DQ
+#define CG_V3_DQ 3      // gather groups (of 32 minimisers, 3 row loads each) kept in flight across a tile
+#endif
 #ifndef CG_V3_MINB
 #define CG_V3_MINB 3
 #endif
@@ -160,7 +163,7 @@ count_kernel_v3(const __grid_constant__ CountParams P) {
             auto LI = [&](uint32_t x) -> uint64_t & { return ring[(qh + x) & uint32_t(WLIST_CAP - 1)]; };
             // Deferred gathers (narrow rows, 3 hash functions, local filter): the row loads of up to DQ groups are issued at the
             // end of a tile and consumed after the NEXT tile's hashing, so the HBM / L2 latency hides behind arithmetic.
-            constexpr int DQ = (MODE == 0) ? 3 : 0;
+            constexpr int DQ = (MODE == 0) ? CG_V3_DQ : 0;
             uint32_t dq_w[DQ ? DQ : 1][3], dq_sh[DQ ? DQ : 1];
             uint32_t ndq = 0;
             const bool can_defer = DQ && P.hash_funs == 3 && P.n_parts == 0;

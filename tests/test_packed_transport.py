@@ -152,3 +152,48 @@ def test_many_bins_and_other_kernels_on_packed_input():
     common.assert_parity(gpu.count_batch(bases, seg_off), idx.classify_batch(bases, seg_off))
     assert gpu.info().last_packed == 0
     gpu.close()
+
+
+@pytest.mark.gpu
+def test_random_ragged_batches_agree_across_transports(small):
+    """Seeded random batches (lengths from one base to several tiles, random alphabets incl. N runs and lower case, random
+    pairing): ASCII and packed transport give the same integers as each other and as the oracle."""
+    idx, refs, gpu = small
+    rng = np.random.default_rng(2024)
+    alphabets = [b"ACGT", b"ACGTN", b"acgtACGT", b"AC", b"ACGTRYKM"]
+    for trial in range(6):
+        pieces = []
+        for _ in range(int(rng.integers(20, 80))):
+            ln = int(rng.choice([rng.integers(0, 64), rng.integers(64, 800), rng.integers(800, 6000)]))
+            kind = rng.integers(0, 4)
+            if kind == 0:
+                st = int(rng.integers(0, 300_000 - ln))
+                p = refs[int(rng.integers(0, 2))][st:st + ln].copy()
+            elif kind == 1:
+                p = rng.choice(np.frombuffer(alphabets[int(rng.integers(0, len(alphabets)))], np.uint8), ln)
+            elif kind == 2:
+                unit = rng.choice(np.frombuffer(b"ACGT", np.uint8), int(rng.integers(1, 30)))
+                p = np.tile(unit, ln // len(unit) + 1)[:ln]
+            else:
+                st = int(rng.integers(0, 300_000 - ln))
+                p = refs[0][st:st + ln].copy()
+                if ln > 40:
+                    a = int(rng.integers(0, ln - 20))
+                    p[a:a + int(rng.integers(1, 20))] = ord("N")
+            pieces.append(np.ascontiguousarray(p, np.uint8))
+        paired = bool(trial & 1)
+        if paired and len(pieces) & 1:
+            pieces.pop()
+        bases, seg_off = common.ragged_batch(rng, pieces)
+        read_seg = np.arange(0, len(pieces) + 1, 2, dtype=np.uint32) if paired else None
+        n = len(pieces) // 2 if paired else len(pieces)
+        mq, cr = common.scalars(n, rng)
+        seglen = np.diff(seg_off)
+        length = (np.add.reduceat(seglen, read_seg[:-1]) if paired else seglen).astype(np.uint32)
+        want = idx.classify_batch(bases, seg_off, read_seg=read_seg, mean_q=mq, compression=cr)
+        for mode in (1, 0):
+            gpu.set_host_pack(mode)
+            got = gpu.classify_batch(bases, seg_off, mq, cr, length, read_seg=read_seg)
+            common.assert_parity(got, want)
+            assert gpu.info().last_packed == (mode if len(bases) else 0)
+    gpu.set_host_pack(-1)
