@@ -86,10 +86,11 @@ struct cg_handle {
     // event that says its last chunk has been copied out
     bool staged_packed = false;
     struct PackStage { void *p = nullptr; size_t cap = 0; cudaEvent_t done = nullptr; bool armed = false; } pack;
+    int async_gather_mode = -1;   // -1: by filter size, 0 / 1: forced (env CHARON_ASYNC_GATHER, test hook)
     int host_pack_mode = -1;      // -1: automatic (thread pool of at least 8), 0: never, 1: whenever the (19, 41) kernels apply
     // launch config
     int grid_per_sm = 1;
-    int warp_grid_per_sm = 1;
+    int warp_grid_per_sm = 1, warp_grid_per_sm_ag = 1;   // resident CTAs per SM of the warp kernel (register / cp.async gather carrier)
     uint64_t staged_max_read_len = 0;
     bool force_cta = false;       // test hook: CTA-per-read kernel for every read
     bool force_generic = false;   // test hook: run the any-(k,w) kernel even when the specialised one applies
@@ -151,6 +152,8 @@ int fail(cg_handle *h, int code, const char *fmt, ...) {
 
 uint32_t ipow5(uint32_t e) { uint32_t r = 1; while (e--) r *= 5u; return r; }
 
+// B200 has 126 MB of L2: a filter below this stays resident next to the streamed bases and plain loads are cheaper
+constexpr size_t ASYNC_GATHER_MIN_FILTER = size_t(96) << 20;
 cgk::CountParams make_params(cg_handle *h) {
     cgk::CountParams P{};
     P.bases = h->bases.as<uint8_t>();
@@ -170,7 +173,8 @@ cgk::CountParams make_params(cg_handle *h) {
     P.long_read_min = 0; P.long_only = 0;
     P.dbg_out = nullptr; P.dbg_cap = 0; P.dbg_n = nullptr;
     P.n_parts = h->n_parts; P.my_part = h->my_part; P.rows_per_part = h->rows_per_part; P.packed = h->staged_packed ? 1 : 0;
-    P.part_pad = 0;
+    P.async_gather = h->async_gather_mode < 0 ? (h->filter_bytes > ASYNC_GATHER_MIN_FILTER ? 1 : 0) : uint32_t(h->async_gather_mode);
+    if (h->hash_funs != 3 || h->n_parts || h->mode != 0) P.async_gather = 0;   // the cp.async carrier exists for the deferred-gather case only
     for (int i = 0; i < CG_MAX_PARTS; ++i) P.part_base[i] = h->part_base[i];
     return P;
 }
@@ -208,22 +212,22 @@ template <int MODE> int occupancy_fast() {
 }
 // warp-per-read kernel (count_kernel_v3): SMALL = at most 4 bins (register tallies, no per-warp counter arrays)
 constexpr unsigned long long LONG_READ_MIN = 65536;   // reads at least this long go to the CTA-per-read kernel
-template <int MODE, bool SMALL> cudaError_t launch_count_warp(cg_handle *h, const cgk::CountParams &P, int grid) {
-    using C = cgk::V3Cfg<FAST_K, FAST_WV, SMALL>;
+template <int MODE, bool SMALL, bool AG = false> cudaError_t launch_count_warp(cg_handle *h, const cgk::CountParams &P, int grid) {
+    using C = cgk::V3Cfg<FAST_K, FAST_WV, SMALL, AG>;
     static bool attr_done = false;
     if (!attr_done) {
-        cudaError_t e = cudaFuncSetAttribute(cgk::count_kernel_v3<MODE, FAST_K, FAST_WV, SMALL>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(C::SMEM));
+        cudaError_t e = cudaFuncSetAttribute(cgk::count_kernel_v3<MODE, FAST_K, FAST_WV, SMALL, AG>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(C::SMEM));
         if (e != cudaSuccess) return e;
         attr_done = true;
     }
-    cgk::count_kernel_v3<MODE, FAST_K, FAST_WV, SMALL><<<grid, cgk::WARPS3 * 32, C::SMEM, h->stream>>>(P);
+    cgk::count_kernel_v3<MODE, FAST_K, FAST_WV, SMALL, AG><<<grid, cgk::WARPS3 * 32, C::SMEM, h->stream>>>(P);
     return cudaGetLastError();
 }
-template <int MODE, bool SMALL> int occupancy_warp() {
-    using C = cgk::V3Cfg<FAST_K, FAST_WV, SMALL>;
+template <int MODE, bool SMALL, bool AG = false> int occupancy_warp() {
+    using C = cgk::V3Cfg<FAST_K, FAST_WV, SMALL, AG>;
     int n = 0;
-    cudaFuncSetAttribute(cgk::count_kernel_v3<MODE, FAST_K, FAST_WV, SMALL>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(C::SMEM));
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, cgk::count_kernel_v3<MODE, FAST_K, FAST_WV, SMALL>, cgk::WARPS3 * 32, C::SMEM);
+    cudaFuncSetAttribute(cgk::count_kernel_v3<MODE, FAST_K, FAST_WV, SMALL, AG>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(C::SMEM));
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, cgk::count_kernel_v3<MODE, FAST_K, FAST_WV, SMALL, AG>, cgk::WARPS3 * 32, C::SMEM);
     return n;
 }
 template <int MODE> int occupancy_mode() {
@@ -247,10 +251,13 @@ int launch_count(cg_handle *h, const cgk::CountParams &P) {
         cgk::CountParams Q = P;
         const bool dispatch = Q.seg_len == nullptr;          // index-build chunks are all handled by the warp kernel
         Q.long_read_min = dispatch ? LONG_READ_MIN : 0;
-        const int wgrid = int(std::min<uint64_t>(uint64_t(h->sm_count) * h->warp_grid_per_sm, (uint64_t(P.n_reads) + cgk::WARPS3 - 1) / cgk::WARPS3));
+        const int wgrid = int(std::min<uint64_t>(uint64_t(h->sm_count) * (Q.async_gather && h->mode == 0 ? h->warp_grid_per_sm_ag : h->warp_grid_per_sm), (uint64_t(P.n_reads) + cgk::WARPS3 - 1) / cgk::WARPS3));
         const bool small = h->bins <= 4;
         switch (h->mode) {
-            case 0: e = small ? launch_count_warp<0, true>(h, Q, wgrid) : launch_count_warp<0, false>(h, Q, wgrid); break;
+            case 0:   // narrow rows: the deferred gathers fly as cp.async when the filter is beyond L2 (count_kernel_v3.cuh)
+                if (Q.async_gather) e = small ? launch_count_warp<0, true, true>(h, Q, wgrid) : launch_count_warp<0, false, true>(h, Q, wgrid);
+                else e = small ? launch_count_warp<0, true>(h, Q, wgrid) : launch_count_warp<0, false>(h, Q, wgrid);
+                break;
             case 1: e = launch_count_warp<1, false>(h, Q, wgrid); break;
             case 2: e = launch_count_warp<2, false>(h, Q, wgrid); break;
             default: e = launch_count_warp<3, false>(h, Q, wgrid); break;

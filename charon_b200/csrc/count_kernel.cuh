@@ -52,7 +52,7 @@ struct CountParams {
     // allocation on GPU p; remote parts are NVLink peer mappings.  n_parts == 0: `filter` is the whole (replicated) filter.
     uint32_t n_parts, my_part;
     uint32_t rows_per_part;             // rows are < 2^32 (bin_size <= 2^32 - 3)
-    uint32_t part_pad;
+    uint32_t async_gather;              // host-side choice of the warp kernel's AG instantiation (filter larger than L2); not read on the device
     uint32_t packed;                    // bases are 4-bit dna5 ranks, two per byte (host_pack.hpp); only the (19, 41) kernels
     const void *part_base[CG_MAX_PARTS];
 };

@@ -15,7 +15,10 @@ namespace cgk {
 #define CG_V3_WARPS 4
 #endif
 #ifndef CG_V3_DQ
-#define CG_V3_DQ 3      // gather groups (of 32 minimisers, 3 row loads each) kept in flight across a tile
+#define CG_V3_DQ 3      // gather groups (of 32 minimisers, 3 row loads each) kept in flight across a tile, in registers
+#endif
+#ifndef CG_V3_DQA
+#define CG_V3_DQA 3     // the same, when they fly as cp.async into shared memory (template parameter AG)
 #endif
 #ifndef CG_V3_MINB
 #define CG_V3_MINB 3
@@ -23,7 +26,7 @@ namespace cgk {
 constexpr int WARPS3 = CG_V3_WARPS;    // warps per CTA (independent of each other)
 constexpr int WLIST_CAP = 256;         // emission ring of a warp (power of two; a tile emits ~60 entries, up to two tiles' worth wait in it)
 
-template <int KK, int WW, bool SMALL> struct V3Cfg {
+template <int KK, int WW, bool SMALL, bool AG = false> struct V3Cfg {
     static constexpr int NK = 32 * WW;            // k-mers per warp tile
     static constexpr int TW = 31 * WW;            // windows per warp tile (incl. the context window)
     static constexpr int NB = NK + KK - 1;        // bases per warp tile
@@ -31,17 +34,18 @@ template <int KK, int WW, bool SMALL> struct V3Cfg {
     static constexpr int NVL = (NVEC + 31) / 32;          // vectors per lane
     static constexpr int NCNT = SMALL ? 8 : 256;
     static constexpr int CODES = ((32 + 16 * NVL * 32 + 64) + 15) / 16 * 16;
+    static constexpr int GQ = AG ? CG_V3_DQA * 3 * 32 * 16 : 0;   // landing slots of the asynchronous gathers: 16 bytes per (group, hash function, lane)
     static constexpr int RAW = NVL * 32 * 16;     // cp.async staging of the next tile's bases (ASCII, or 32 rank nibbles per vector)
     static_assert((31 + NB + 31) / 32 <= 32, "packed transport: one vector per lane must cover a tile");
     // a lane that overruns its PRIV_CAP slots (such a tile is redone exactly) spills into its right neighbour's slots; lane 31
     // spills into PRIV_GUARD, never into the list, whose head holds minimisers still waiting for a full gather group
     static constexpr int PRIV_GUARD = WW + 1 - PRIV_CAP > 0 ? WW + 1 - PRIV_CAP : 0;
     static constexpr size_t WARP_BYTES = size_t(NK) * 8 + (size_t(32) * PRIV_CAP + PRIV_GUARD) * 8 + size_t(WLIST_CAP) * 8 + size_t(NCNT) * 8 + 32 +
-                                         size_t(NCNT) * 4 * 2 + CODES + RAW;
+                                         size_t(NCNT) * 4 * 2 + CODES + RAW + GQ;
     static constexpr size_t SMEM = 512 + WARPS3 * WARP_BYTES;
 };
 
-template <int MODE, int KK, int WW, bool SMALL>
+template <int MODE, int KK, int WW, bool SMALL, bool AG = false>
 #ifdef CG_V3_MAXNREG
 __global__ void __maxnreg__(CG_V3_MAXNREG)
 #else
@@ -49,7 +53,7 @@ __global__ void __launch_bounds__(WARPS3 * 32, CG_V3_MINB)
 #endif
 count_kernel_v3(const __grid_constant__ CountParams P) {
     using C2 = V2Cfg<KK, WW>;
-    using C = V3Cfg<KK, WW, SMALL>;
+    using C = V3Cfg<KK, WW, SMALL, AG && MODE == 0>;
     constexpr int NW = ModeTraits<MODE>::NW;
     constexpr int KL = C2::KL, KH = C2::KH;
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -93,6 +97,7 @@ count_kernel_v3(const __grid_constant__ CountParams P) {
     const bool packed = P.packed != 0;
     const uint8_t *const gbases = P.bases;
     uint64_t pf_tag = 0;
+    const uint32_t gq_s = uint32_t(__cvta_generic_to_shared(S.codes + C::CODES + C::RAW)) + lane * 16u;
     const uint32_t raw_s = uint32_t(__cvta_generic_to_shared(raw));
     auto tile_head = [&](uint64_t G) -> uint32_t {
         return packed ? uint32_t(G & 31u) : uint32_t(reinterpret_cast<uintptr_t>(gbases + G) & 15u);
@@ -156,30 +161,61 @@ count_kernel_v3(const __grid_constant__ CountParams P) {
 
             // S.list is a ring: `pend` emitted values starting at `qh` wait to be queried (warp-uniform); only full groups of 32 are
             // queried per tile, the rest waits for the next tile's emissions.
-            // (Measured and dropped: pulling the rows into L2 one tile ahead with prefetch.global.L2 made the human-scale launch
-            // 50 % slower; fetching them with 4-byte cp.async into shared memory 15 % slower.)
             uint32_t pend = 0, qh = 0;
             uint64_t *const ring = S.list;
             auto LI = [&](uint32_t x) -> uint64_t & { return ring[(qh + x) & uint32_t(WLIST_CAP - 1)]; };
-            // Deferred gathers (narrow rows, 3 hash functions, local filter): the row loads of up to DQ groups are issued at the
-            // end of a tile and consumed after the NEXT tile's hashing, so the HBM / L2 latency hides behind arithmetic.
+            // Deferred gathers (narrow rows, 3 hash functions, local filter): the row fetches of the first full groups are issued
+            // at the end of a tile and consumed after the NEXT tile's hashing, so the HBM / L2 latency hides behind arithmetic.
+            // Two carriers = two instantiations (template parameter AG; the host launches AG when the filter does not fit in L2 —
+            // one kernel with a run-time switch between them was 20-50 % slower on both):
+            //  * registers (plain loads, up to DQ groups): cheapest in instructions, best while the rows hit L2; but ptxas
+            //    recycles the loads' scoreboard at the top of the next tile, so a DRAM-latency load is waited for there;
+            //  * shared memory (16-byte cp.async.cg of the aligned chunk holding the row word, up to DQA groups): completion is
+            //    tracked per commit group, nothing forces an early wait; +4 % on an L2-resident filter, -4.5 % on an 0.86 GB one.
+            // With AG every tile commits exactly two cp.async groups, in this order: the next tile's bases (phase 0), the gathers
+            // (end of phase 3); either may be empty.  Without AG only the bases are committed — the extra commits / wait_group 1
+            // alone made the register carrier 20-50 % slower, so the two structures are kept apart at compile time.  (Measured and dropped: 4-byte cp.async.ca, prefetch.global.L2.)
             constexpr int DQ = (MODE == 0) ? CG_V3_DQ : 0;
-            uint32_t dq_w[DQ ? DQ : 1][3], dq_sh[DQ ? DQ : 1];
+            constexpr int DQA = (MODE == 0) ? CG_V3_DQA : 0;
+            constexpr int DQM = DQ > DQA ? DQ : DQA;
+            uint32_t dq_w[DQ ? DQ : 1][3], dq_sh[DQM ? DQM : 1];
             uint32_t ndq = 0;
             const bool can_defer = DQ && P.hash_funs == 3 && P.n_parts == 0;
-            auto dq_finish = [&]() {
+            constexpr bool ag = AG && (MODE == 0);
+            auto dq_finish = [&](bool bases_group_behind) {
                 if (DQ) {
                     const uint32_t rb = 1u << P.row_shift;
                     const uint32_t msk = rb >= 32 ? 0xFFFFFFFFu : ((1u << rb) - 1u);
-#pragma unroll
-                    for (int g = 0; g < DQ; ++g)
-                        if (g < int(ndq)) {
-                            Mask<NW> m;
-#pragma unroll
-                            for (int j = 1; j < NW; ++j) m.w[j] = 0;
-                            m.w[0] = ((dq_w[g][0] >> (dq_sh[g] & 31u)) & (dq_w[g][1] >> ((dq_sh[g] >> 5) & 31u)) & (dq_w[g][2] >> (dq_sh[g] >> 10))) & msk;
-                            T.add(m, bm, small_bins, do_tot, do_unq, S);
+                    if (ag) {
+                        if (ndq) {
+                            if (bases_group_behind) asm volatile("cp.async.wait_group 1;" ::: "memory");
+                            else asm volatile("cp.async.wait_group 0;" ::: "memory");
                         }
+#pragma unroll
+                        for (int g = 0; g < DQA; ++g)
+                            if (g < int(ndq)) {
+                                const uint32_t sh = dq_sh[g];
+                                uint32_t w[3];
+#pragma unroll
+                                for (int i = 0; i < 3; ++i)
+                                    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w[i]) : "r"(gq_s + uint32_t(g * 3 + i) * 512u + (((sh >> (15 + 2 * i)) & 3u) << 2)) : "memory");
+                                Mask<NW> m;
+#pragma unroll
+                                for (int j = 1; j < NW; ++j) m.w[j] = 0;
+                                m.w[0] = ((w[0] >> (sh & 31u)) & (w[1] >> ((sh >> 5) & 31u)) & (w[2] >> ((sh >> 10) & 31u))) & msk;
+                                T.add(m, bm, small_bins, do_tot, do_unq, S);
+                            }
+                    } else {
+#pragma unroll
+                        for (int g = 0; g < DQ; ++g)
+                            if (g < int(ndq)) {
+                                Mask<NW> m;
+#pragma unroll
+                                for (int j = 1; j < NW; ++j) m.w[j] = 0;
+                                m.w[0] = ((dq_w[g][0] >> (dq_sh[g] & 31u)) & (dq_w[g][1] >> ((dq_sh[g] >> 5) & 31u)) & (dq_w[g][2] >> ((dq_sh[g] >> 10) & 31u))) & msk;
+                                T.add(m, bm, small_bins, do_tot, do_unq, S);
+                            }
+                    }
                 }
                 ndq = 0;
             };
@@ -214,8 +250,17 @@ count_kernel_v3(const __grid_constant__ CountParams P) {
                     const uint64_t G = sbase + g0;
                     const uint32_t head = tile_head(G);
                     const uint32_t nvec = tile_nvec(head, nb);
-                    if (pf_tag != G + 1) prefetch(G, nb);             // not predicted: load now
-                    asm volatile("cp.async.wait_all;" ::: "memory");
+                    if (AG && MODE == 0) {
+                        if (pf_tag != G + 1) {                        // not predicted: load now, wait for everything
+                            prefetch(G, nb);
+                            asm volatile("cp.async.wait_group 0;" ::: "memory");
+                        } else {
+                            asm volatile("cp.async.wait_group 1;" ::: "memory");   // the bases; the previous tile's gathers (committed later) may still fly
+                        }
+                    } else {
+                        if (pf_tag != G + 1) prefetch(G, nb);         // not predicted: load now
+                        asm volatile("cp.async.wait_all;" ::: "memory");
+                    }
                     __syncwarp();                                      // staging complete for every lane; previous tile's readers of codes are done
                     if (packed) {
                         if (lane < nvec) {   // a tile is at most 26 vectors of 32 bases
@@ -245,7 +290,10 @@ count_kernel_v3(const __grid_constant__ CountParams P) {
                         prefetch(sbase + g1, tw1 + WW - 1 + KK - 1);
                     } else if (last_pass && seg + 1 == seg1 && next_read_nb) {
                         prefetch(next_read_G, next_read_nb);
-                    } else pf_tag = 0;
+                    } else {
+                        pf_tag = 0;
+                        if (AG && MODE == 0) asm volatile("cp.async.commit_group;" ::: "memory");   // empty: keeps the two-groups-per-tile order
+                    }
                     __syncwarp();
                     // ---- phase 1: rolling canonical hash of the lane's block, prefix minima -> smem -------------------
                     const uint32_t k0 = lane * WW;
@@ -355,22 +403,42 @@ count_kernel_v3(const __grid_constant__ CountParams P) {
                         const uint32_t fullg = (pend + nl) & ~31u;
                         uint32_t first_now = 0;   // groups below this index go through the deferred queue
                         if (can_defer) {
-                            dq_finish();          // loads issued one tile ago
+                            dq_finish(true);      // issued one tile ago; this tile's bases group was committed after them
                             const uint32_t ngroups = fullg >> 5;
+                            if (ag) {
 #pragma unroll
-                            for (int g = 0; g < DQ; ++g)
-                                if (uint32_t(g) < ngroups) {
-                                    const uint64_t value = LI(g * 32 + lane);
-                                    uint32_t sh = 0;
+                                for (int g = 0; g < DQA; ++g)
+                                    if (uint32_t(g) < ngroups) {
+                                        const uint64_t value = LI(g * 32 + lane);
+                                        uint32_t sh = 0;
 #pragma unroll
-                                    for (int i = 0; i < 3; ++i) {
-                                        const uint32_t row = ibf_row32(value, c_ibf_seeds[i], P.hash_shift, uint32_t(P.bin_size));
-                                        dq_w[g][i] = ldg_na_u32(reinterpret_cast<const uint32_t *>(P.filter) + (row >> (5u - P.row_shift)), pol_filter);
-                                        sh |= ((row << P.row_shift) & 31u) << (5 * i);
+                                        for (int i = 0; i < 3; ++i) {
+                                            const uint32_t row = ibf_row32(value, c_ibf_seeds[i], P.hash_shift, uint32_t(P.bin_size));
+                                            const uint32_t word = row >> (5u - P.row_shift);
+                                            asm volatile("cp.async.cg.shared.global.L2::cache_hint [%0], [%1], 16, %2;" ::"r"(gq_s + uint32_t(g * 3 + i) * 512u),
+                                                         "l"(reinterpret_cast<const uint32_t *>(P.filter) + (word & ~3u)), "l"(pol_filter)
+                                                         : "memory");
+                                            sh |= (((row << P.row_shift) & 31u) << (5 * i)) | ((word & 3u) << (15 + 2 * i));
+                                        }
+                                        dq_sh[g] = sh;
                                     }
-                                    dq_sh[g] = sh;
-                                }
-                            ndq = ngroups < uint32_t(DQ) ? ngroups : uint32_t(DQ);
+                                ndq = ngroups < uint32_t(DQA) ? ngroups : uint32_t(DQA);
+                            } else {
+#pragma unroll
+                                for (int g = 0; g < DQ; ++g)
+                                    if (uint32_t(g) < ngroups) {
+                                        const uint64_t value = LI(g * 32 + lane);
+                                        uint32_t sh = 0;
+#pragma unroll
+                                        for (int i = 0; i < 3; ++i) {
+                                            const uint32_t row = ibf_row32(value, c_ibf_seeds[i], P.hash_shift, uint32_t(P.bin_size));
+                                            dq_w[g][i] = ldg_na_u32(reinterpret_cast<const uint32_t *>(P.filter) + (row >> (5u - P.row_shift)), pol_filter);
+                                            sh |= ((row << P.row_shift) & 31u) << (5 * i);
+                                        }
+                                        dq_sh[g] = sh;
+                                    }
+                                ndq = ngroups < uint32_t(DQ) ? ngroups : uint32_t(DQ);
+                            }
                             first_now = ndq * 32;
                         }
                         for (uint32_t i = first_now + lane; i < fullg; i += 32) {
@@ -380,12 +448,13 @@ count_kernel_v3(const __grid_constant__ CountParams P) {
                         qh = (qh + fullg) & uint32_t(WLIST_CAP - 1);
                         pend = pend + nl - fullg;
                     }
+                    if (AG && MODE == 0) asm volatile("cp.async.commit_group;" ::: "memory");   // the gathers of this tile (possibly none)
                     if (last_tile) break;
                     g0 += Tw - 1;
                     first = false;
                 }  // tiles
             }      // segments
-            dq_finish();
+            dq_finish(false);
             if (pend) {   // flush what is still waiting at the end of this pass
                 __syncwarp();
                 for (uint32_t i = lane; i < pend; i += 32) {

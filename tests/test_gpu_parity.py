@@ -369,3 +369,36 @@ def test_full_size_batch_properties():
     want = idx.classify_batch(bases[:k * L], seg_off[:k + 1], mean_q=mq[:k], compression=cr[:k])
     common.assert_parity({key: whole[key][:k] for key in ("num_hashes", "counts", "unique_counts", "call", "confidence", "prob")}, want)
     gpu.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("mode", ["1", "0"])
+def test_both_gather_carriers(monkeypatch, mode):
+    """The deferred filter gathers travel either in registers (plain loads) or as cp.async into shared memory; the library picks
+    by filter size (only filters beyond L2 take the second), so the small test filters force each in turn (CHARON_ASYNC_GATHER)."""
+    import charon_b200
+    monkeypatch.setenv("CHARON_ASYNC_GATHER", mode)
+    idx, refs = common.build_oracle_index([300_000, 300_000], [0, 1], ["host", "microbial"], seed=11)
+    gpu = common.gpu_from_oracle(idx)
+    try:
+        gpu.set_model(charon_b200.DehostOptions(), host_index=idx.host_index)
+        rng = np.random.default_rng(5)
+        # long enough reads for several tiles with more than DQA full groups in flight, plus ragged / short / paired ones
+        bases, seg_off, _ = common.fixed_length_batch(31, refs, [0.45, 0.45], 1500, 9001)
+        mq, cr = common.scalars(1500, rng)
+        want = idx.classify_batch(bases, seg_off, mean_q=mq, compression=cr)
+        for pack in (1, 0):
+            gpu.set_host_pack(pack)
+            common.assert_parity(gpu.classify_batch(bases, seg_off, mq, cr, np.full(1500, 9001, np.uint32)), want)
+        pieces = [refs[int(rng.integers(0, 2))][s:s + ln].copy() for ln in [0, 5, 41, 800, 2985, 2986, 30_000, 70_000, 1426 + 40, 19, 64, 12_000]
+                  for s in [int(rng.integers(0, 200_000))]]
+        pieces.append(np.frombuffer(b"ACGTTGCA" * 3000, np.uint8))       # tie tiles: the exact path runs between deferred groups
+        pieces.append(np.frombuffer(b"A" * 9000, np.uint8))
+        b2, so2 = common.ragged_batch(rng, pieces)
+        read_seg = np.arange(0, len(pieces) + 1, 2, dtype=np.uint32)
+        want2 = idx.classify_batch(b2, so2, read_seg=read_seg)
+        got2 = gpu.count_batch(b2, so2, read_seg=read_seg)
+        common.assert_parity(got2, want2)
+        common.assert_parity(gpu.count_batch(b2, so2), idx.classify_batch(b2, so2))
+    finally:
+        gpu.close()
