@@ -28,7 +28,10 @@ constexpr int NT2 = 128;
 #define CG_V2_LIST_CAP 1024
 #endif
 constexpr int LIST_CAP = CG_V2_LIST_CAP;   // compacted emission list of a tile (expected ~265 entries)
-constexpr int PRIV_CAP = 8;      // per-thread emission slots (expected ~2 per 23 windows); overrun => exact path
+#ifndef CG_PRIV_CAP
+#define CG_PRIV_CAP 8
+#endif
+constexpr int PRIV_CAP = CG_PRIV_CAP;      // per-thread emission slots (expected ~2 per 23 windows); overrun => exact path
 constexpr uint64_t VMAX = ~0ull;   // never a real value: k <= 26 keeps the top 3 bits of v equal to the seed's (100b)
 
 constexpr uint32_t cpow5(int e) { uint32_t r = 1; for (int i = 0; i < e; ++i) r *= 5u; return r; }

@@ -24,7 +24,10 @@ namespace cgk {
 #define CG_V3_MINB 3
 #endif
 constexpr int WARPS3 = CG_V3_WARPS;    // warps per CTA (independent of each other)
-constexpr int WLIST_CAP = 256;         // emission ring of a warp (power of two; a tile emits ~60 entries, up to two tiles' worth wait in it)
+#ifndef CG_V3_WLIST_CAP
+#define CG_V3_WLIST_CAP 256
+#endif
+constexpr int WLIST_CAP = CG_V3_WLIST_CAP;         // emission ring of a warp (power of two; a tile emits ~60 entries, up to two tiles' worth wait in it)
 
 template <int KK, int WW, bool SMALL, bool AG = false> struct V3Cfg {
     static constexpr int NK = 32 * WW;            // k-mers per warp tile
@@ -43,6 +46,8 @@ template <int KK, int WW, bool SMALL, bool AG = false> struct V3Cfg {
     static constexpr size_t WARP_BYTES = size_t(NK) * 8 + (size_t(32) * PRIV_CAP + PRIV_GUARD) * 8 + size_t(WLIST_CAP) * 8 + size_t(NCNT) * 8 + 32 +
                                          size_t(NCNT) * 4 * 2 + CODES + RAW + GQ;
     static constexpr size_t SMEM = 512 + WARPS3 * WARP_BYTES;
+    static_assert(((size_t(32) * PRIV_CAP + PRIV_GUARD) * 8) % 16 == 0 && CODES % 16 == 0 && WARP_BYTES % 16 == 0,
+                  "the staging vectors behind the slots need 16-byte alignment");
 };
 
 template <int MODE, int KK, int WW, bool SMALL, bool AG = false>
