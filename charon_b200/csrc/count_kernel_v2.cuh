@@ -82,6 +82,20 @@ __device__ __forceinline__ uint32_t encode4(const uint8_t *lut, uint32_t w) {   
            (uint32_t(lut[w >> 24]) << 24);
 }
 __device__ __forceinline__ uint64_t umin64(uint64_t a, uint64_t b) { return a < b ? a : b; }
+// The same minimum with ONE compare (DSETP + 2 SEL instead of ISETP + ISETP.EX + 2 SEL): every real value carries the seed's
+// top bits (1 00.. for k <= 26), i.e. read as a double it is negative and finite (or a negative denormal), and for those
+// the IEEE order is the reverse of the unsigned order of the bit patterns.  VMAX (all ones) reads as NaN: it may only be
+// passed as `a` (an unordered compare is false and selects b).  Used on the hot min chains; CG_UMIN_INT=1 switches back.
+#ifndef CG_UMIN_INT
+#define CG_UMIN_INT 0
+#endif
+__device__ __forceinline__ uint64_t umin64h(uint64_t a, uint64_t b) {
+#if CG_UMIN_INT
+    return a < b ? a : b;
+#else
+    return __longlong_as_double((long long)a) > __longlong_as_double((long long)b) ? a : b;
+#endif
+}
 // Store through a 32-bit shared-space address.  A moving generic pointer costs a 64-bit add next to the address the STS uses;
 // deliberately no "memory" clobber (the window-minimum loads around it must stay free to move): the caller fences once.
 __device__ __forceinline__ void st_shared_u64(uint32_t addr, uint64_t v) { asm volatile("st.shared.u64 [%0], %1;" ::"r"(addr), "l"(v)); }
@@ -162,12 +176,12 @@ __device__ __forceinline__ void p2_block(uint64_t (&v)[WW], uint64_t vleft, cons
 #pragma unroll
     for (int j = WW - 1; j >= 0; --j) {
         const bool wv = !EDGE || (k0 + j < Tw);
-        if (j < WW - 1) { tie = tie | (lo32(v[j]) == lo32(sv)); sv = umin64(sv, v[j]); }
+        if (j < WW - 1) { tie = tie | (lo32(v[j]) == lo32(sv)); sv = umin64h(sv, v[j]); }
         uint64_t mw = sv;
         if (j >= 1) {
             const uint64_t npm = (EDGE && !wv) ? VMAX : next[j - 1];
             tie = tie | ((lo32(npm) == lo32(sv)) & wv);
-            mw = umin64(sv, npm);
+            mw = umin64h(npm, sv);   // npm may be VMAX: first operand
         }
         const uint64_t leaving = j >= 1 ? v[j >= 1 ? j - 1 : 0] : vleft;
         tie = tie | ((lo32(leaving) == lo32(mw)) & wv);

@@ -320,7 +320,7 @@ count_kernel_v3(const __grid_constant__ CountParams P) {
                         for (int j = KK; j-- > KL;) RHi = RHi * 5u + (cp[j] >> 4);
                         {
                             const uint64_t f = (uint64_t(Hi) * C2::P_KL + Lo) ^ seed, rc = (uint64_t(RHi) * C2::P_KL + RLo) ^ seed;
-                            vleft = k0 > 0 ? umin64(f, rc) : VMAX;
+                            vleft = k0 > 0 ? umin64h(f, rc) : VMAX;
                         }
 #pragma unroll
                         for (int j = 0; j < WW; ++j) {
@@ -332,7 +332,7 @@ count_kernel_v3(const __grid_constant__ CountParams P) {
                                 RHi = (RHi - (bl >> 4)) * INV5 + (bK >> 4) * C2::P_HI_TOP;
                             }
                             const uint64_t f = (uint64_t(Hi) * C2::P_KL + Lo) ^ seed, rc = (uint64_t(RHi) * C2::P_KL + RLo) ^ seed;
-                            v[j] = umin64(f, rc);
+                            v[j] = umin64h(f, rc);
                         }
                         // k-mers at or beyond nk are NOT masked: every valid window w < Tw = nk - WW + 1 only covers k-mers
                         // w .. w+WW-1 <= nk-1 (own suffix + the right neighbour's prefix up to that index), the tie flags below
@@ -343,10 +343,10 @@ count_kernel_v3(const __grid_constant__ CountParams P) {
                         for (int j = 1; j < WW; ++j) {
                             if (j == WW - 1) {
                                 tie = tie | (lo32(vleft) == lo32(pm));
-                                m_prevwin = umin64(vleft, pm);
+                                m_prevwin = umin64h(vleft, pm);
                             }
                             tie = tie | (lo32(v[j]) == lo32(pm));   // k-mers past nk can only add a spurious exact-path tile
-                            pm = umin64(pm, v[j]);
+                            pm = umin64h(pm, v[j]);
                             S.arr[k0 + j] = pm;
                         }
                         if (WW == 1) m_prevwin = vleft;
