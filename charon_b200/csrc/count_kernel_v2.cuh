@@ -96,6 +96,17 @@ __device__ __forceinline__ uint64_t umin64h(uint64_t a, uint64_t b) {
     return __longlong_as_double((long long)a) > __longlong_as_double((long long)b) ? a : b;
 #endif
 }
+// a != b with one compare (DSETP.NEU): distinct real values are distinct doubles (all negative, never -0 vs +0).
+__device__ __forceinline__ bool neq64h(uint64_t a, uint64_t b) {
+#if CG_UMIN_INT
+    return a != b;
+#else
+    return __longlong_as_double((long long)a) != __longlong_as_double((long long)b);
+#endif
+}
+#ifndef CG_TIE_LEAVING_ONLY
+#define CG_TIE_LEAVING_ONLY 1   // see p2_block
+#endif
 // Store through a 32-bit shared-space address.  A moving generic pointer costs a 64-bit add next to the address the STS uses;
 // deliberately no "memory" clobber (the window-minimum loads around it must stay free to move): the caller fences once.
 __device__ __forceinline__ void st_shared_u64(uint32_t addr, uint64_t v) { asm volatile("st.shared.u64 [%0], %1;" ::"r"(addr), "l"(v)); }
@@ -166,9 +177,12 @@ __device__ __forceinline__ void scan_window(const uint64_t *arr, uint32_t w, uin
 
 // Phase 2 for one full block.  v[] = the block's 23 values; on return v[0] holds the minimum of window k0.
 // next = prefix minima of the right neighbour block (shared memory).  EDGE: some windows of the block lie beyond Tw.
-// Emission: window w+1 starts a run iff min(w+1) != min(w).  `tie` collects every situation in which positions (not
-// just values) would matter: equal low words between the two operands of any min, or between the value that has just
-// left the window and the new minimum (an equal value exactly W k-mers apart).
+// Emission: window w+1 starts a run iff min(w+1) != min(w).  That rule equals seqan3's "tracked position changed" unless
+// the k-mer that has just left window w carries the value of min(w): if the tracked element is still inside, a newcomer
+// takes over iff it is strictly smaller (min changes) and nothing happens otherwise (min unchanged); if the tracked
+// element left, seqan3 always emits the new rightmost minimum, and the value rule misses that exactly when
+// leaving == min(w).  So `tie` only needs that one test (on low words: a superset).  CG_TIE_LEAVING_ONLY=0 restores the
+// earlier scheme (run starts compared on low words, every min step flagged on equal low words: 3 more ISETP per window).
 template <int WW, bool EDGE>
 __device__ __forceinline__ void p2_block(uint64_t (&v)[WW], uint64_t vleft, const uint64_t *next, uint32_t k0, uint32_t Tw, uint32_t &pa,
                                          bool &tie) {
@@ -176,19 +190,30 @@ __device__ __forceinline__ void p2_block(uint64_t (&v)[WW], uint64_t vleft, cons
 #pragma unroll
     for (int j = WW - 1; j >= 0; --j) {
         const bool wv = !EDGE || (k0 + j < Tw);
-        if (j < WW - 1) { tie = tie | (lo32(v[j]) == lo32(sv)); sv = umin64h(sv, v[j]); }
+        if (j < WW - 1) {
+#if !CG_TIE_LEAVING_ONLY
+            tie = tie | (lo32(v[j]) == lo32(sv));
+#endif
+            sv = umin64h(sv, v[j]);
+        }
         uint64_t mw = sv;
         if (j >= 1) {
             const uint64_t npm = (EDGE && !wv) ? VMAX : next[j - 1];
+#if !CG_TIE_LEAVING_ONLY
             tie = tie | ((lo32(npm) == lo32(sv)) & wv);
+#endif
             mw = umin64h(npm, sv);   // npm may be VMAX: first operand
         }
         const uint64_t leaving = j >= 1 ? v[j >= 1 ? j - 1 : 0] : vleft;
         tie = tie | ((lo32(leaving) == lo32(mw)) & wv);
         if (j < WW - 1) {
+#if CG_TIE_LEAVING_ONLY
+            const bool start = neq64h(mw_next, mw) & (!EDGE || (k0 + j + 1 < Tw));
+#else
             // low words suffice: two DIFFERENT adjacent window minima with equal low words always trip one of the tie flags
             // (old minimum left: `leaving` check; newcomer took over: it met the old minimum in a prefix / suffix / combine step)
             const bool start = (lo32(mw_next) != lo32(mw)) & (!EDGE || (k0 + j + 1 < Tw));
+#endif
             if (start) { st_shared_u64(pa, mw_next); pa += 8u; }   // one predicated STS + one 32-bit add per window
         }
         mw_next = mw;

@@ -377,10 +377,14 @@ count_kernel_v3(const __grid_constant__ CountParams P) {
 #pragma unroll
                         for (int j = 1; j < WW; ++j) {
                             if (j == WW - 1) {
+#if !CG_TIE_LEAVING_ONLY
                                 tie = tie | (lo32(vleft) == lo32(pm));
+#endif
                                 m_prevwin = umin64h(vleft, pm);
                             }
+#if !CG_TIE_LEAVING_ONLY
                             tie = tie | (lo32(v[j]) == lo32(pm));   // k-mers past nk can only add a spurious exact-path tile
+#endif
                             pm = umin64h(pm, v[j]);
                             S.arr[k0 + j] = pm;
                         }
@@ -398,7 +402,7 @@ count_kernel_v3(const __grid_constant__ CountParams P) {
                     if (active && k0 < Tw) {
                         if (k0 + WW <= Tw) p2_block<WW, false>(v, vleft, S.arr + k0 + WW, k0, Tw, pa, tie);
                         else p2_block<WW, true>(v, vleft, S.arr + k0 + WW, k0, Tw, pa, tie);
-                        if (k0 > 0 ? (lo32(v[0]) != lo32(m_prevwin)) : first) { st_shared_u64(pa, v[0]); pa += 8u; }   // low words: see p2_block
+                        if (k0 > 0 ? (CG_TIE_LEAVING_ONLY ? neq64h(v[0], m_prevwin) : (lo32(v[0]) != lo32(m_prevwin))) : first) { st_shared_u64(pa, v[0]); pa += 8u; }   // see p2_block
                     }
                     asm volatile("" ::: "memory");   // the slots were written by st_shared_u64 (no memory clobber of its own): order the reads below
                     const uint32_t cnt = (pa - pa0) >> 3;
