@@ -18,9 +18,10 @@ namespace cgk {
 #define CG_V3_DQ 3      // gather groups (of 32 minimisers, 3 row loads each) kept in flight across a tile, in registers
 #endif
 #ifndef CG_V3_RC_LEFT
-#define CG_V3_RC_LEFT 0 // 1: reverse strand rolled right to left (2 IMAD per limb instead of 3 for the exact division by 5).
-                        // Measured: fewer instructions but SLOWER (4.60 -> 4.77 ms bacterial, 6.62 -> 6.89 ms human-scale; ptxas
-                        // spills twice as much with all 23 values live across both passes).  Parity-tested, kept as a knob.
+#define CG_V3_RC_LEFT 0     // reverse strand rolled right to left (2 IMAD per limb) instead of left to right (exact division by
+#endif                      // 5: 3 per limb).  Fewer instructions, but all 23 values stay live across two passes and ptxas spills
+#ifndef CG_V3_RC_LEFT_AG    // more.  Measured A/B (variants/, two runs each): register-carrier kernel (L2-resident filter) 4.524 ->
+#define CG_V3_RC_LEFT_AG 1  // 4.56 ms = off; cp.async-carrier kernel (filter beyond L2) 6.55 -> 6.48 ms = on.
 #endif
 #ifndef CG_V3_DQA
 #define CG_V3_DQA 3     // the same, when they fly as cp.async into shared memory (template parameter AG)
@@ -319,7 +320,7 @@ count_kernel_v3(const __grid_constant__ CountParams P) {
                         for (int j = 0; j < KH; ++j) Hi = Hi * 5u + (cp[j] & 15u);
 #pragma unroll
                         for (int j = KH; j < KK; ++j) Lo = Lo * 5u + (cp[j] & 15u);
-#if CG_V3_RC_LEFT
+                        if (AG ? CG_V3_RC_LEFT_AG : CG_V3_RC_LEFT) {
                         // The reverse strand is rolled RIGHT TO LEFT (from the block's last k-mer down to k-mer k0-1): moving
                         // left, the complement digits enter at the bottom, so both strands roll with "drop the top digit,
                         // times 5, add" (2 IMAD per limb) and the exact division by 5 (3 per limb) is gone.  v[] holds the
@@ -347,7 +348,7 @@ count_kernel_v3(const __grid_constant__ CountParams P) {
                             const uint64_t f = (uint64_t(Hi) * C2::P_KL + Lo) ^ seed;
                             v[j] = umin64h(f, v[j]);
                         }
-#else
+                        } else {
 #pragma unroll
                         for (int j = KL; j-- > 0;) RLo = RLo * 5u + (cp[j] >> 4);
 #pragma unroll
@@ -368,7 +369,7 @@ count_kernel_v3(const __grid_constant__ CountParams P) {
                             const uint64_t f = (uint64_t(Hi) * C2::P_KL + Lo) ^ seed, rc = (uint64_t(RHi) * C2::P_KL + RLo) ^ seed;
                             v[j] = umin64h(f, rc);
                         }
-#endif
+                        }
                         // k-mers at or beyond nk are NOT masked: every valid window w < Tw = nk - WW + 1 only covers k-mers
                         // w .. w+WW-1 <= nk-1 (own suffix + the right neighbour's prefix up to that index), the tie flags below
                         // are guarded, and windows >= Tw are dropped by the EDGE variant of p2_block / by exact_tile's bound.
