@@ -164,6 +164,8 @@ cgk::CountParams make_params(cg_handle *h) {
     P.kl = std::min<uint32_t>(h->K, 13); P.kh = h->K - P.kl;
     P.p_lo_top = ipow5(P.kl - 1); P.p_hi_top = P.kh ? ipow5(P.kh - 1) : 0; P.p_kl = ipow5(P.kl);
     P.seed = 0x8F3F73B5CF1C9ADEULL;   // seqan3::seed default
+    static_assert((0x8F3F73B5CF1C9ADEULL >> 61) == 4,
+                  "umin64h/neq64h (count_kernel_v2.cuh) read the seeded values as negative finite doubles: top bits 100b");
     P.filter = h->d_filter; P.bin_size = h->bin_size; P.hash_shift = h->hash_shift; P.hash_funs = h->hash_funs;
     P.row_shift = h->row_shift; P.bins = h->bins; P.ncat = h->ncat; P.single_pass = h->single_pass ? 1 : 0;
     P.bin_to_cat = h->d_bin_to_cat;
