@@ -96,6 +96,18 @@ __device__ __forceinline__ uint64_t umin64h(uint64_t a, uint64_t b) {
     return __longlong_as_double((long long)a) > __longlong_as_double((long long)b) ? a : b;
 #endif
 }
+// The two SERIAL chains (running prefix / suffix minimum) may use either flavour: CG_UMIN_CHAIN_INT=1 keeps the integer
+// compare there (shorter dependent latency than a DSETP through the short scoreboard, one more instruction).
+#ifndef CG_UMIN_CHAIN_INT
+#define CG_UMIN_CHAIN_INT 0
+#endif
+__device__ __forceinline__ uint64_t umin64c(uint64_t a, uint64_t b) {
+#if CG_UMIN_CHAIN_INT
+    return a < b ? a : b;
+#else
+    return umin64h(a, b);
+#endif
+}
 // a != b with one compare (DSETP.NEU): distinct real values are distinct doubles (all negative, never -0 vs +0).
 __device__ __forceinline__ bool neq64h(uint64_t a, uint64_t b) {
 #if CG_UMIN_INT
@@ -194,7 +206,7 @@ __device__ __forceinline__ void p2_block(uint64_t (&v)[WW], uint64_t vleft, cons
 #if !CG_TIE_LEAVING_ONLY
             tie = tie | (lo32(v[j]) == lo32(sv));
 #endif
-            sv = umin64h(sv, v[j]);
+            sv = umin64c(sv, v[j]);
         }
         uint64_t mw = sv;
         if (j >= 1) {

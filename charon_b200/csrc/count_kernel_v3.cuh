@@ -386,7 +386,7 @@ count_kernel_v3(const __grid_constant__ CountParams P) {
 #if !CG_TIE_LEAVING_ONLY
                             tie = tie | (lo32(v[j]) == lo32(pm));   // k-mers past nk can only add a spurious exact-path tile
 #endif
-                            pm = umin64h(pm, v[j]);
+                            pm = umin64c(pm, v[j]);
                             S.arr[k0 + j] = pm;
                         }
                         if (WW == 1) m_prevwin = vleft;
