@@ -252,6 +252,34 @@ def test_equal_values_exactly_one_window_apart(small):
             assert np.array_equal(gpu.debug_minimisers(s), np.sort(oracle.minimisers(s))), (period, n)
 
 
+def test_duplicate_values_inside_one_window(small):
+    """The fast path keeps ONE tie test (the k-mer that has just left a window carries that window's minimum, count_kernel_v2.cuh
+    p2_block) and compares run starts on full values.  Stress it with equal canonical values at every distance below, at and
+    above the window length: a 19-mer repeated d bases later, and a 19-mer followed by its reverse complement (same canonical
+    value on the other strand), planted at random offsets so that they also meet block and tile boundaries."""
+    idx, refs, gpu = small
+    rng = random.Random(11)
+    comp = {"A": "T", "C": "G", "G": "C", "T": "A"}
+    rnd = lambda n: "".join(rng.choice("ACGT") for _ in range(n))
+    for mode in (0, 2):   # warp-per-read and CTA-per-read kernels
+        gpu.force_generic(mode)
+        try:
+            for d in list(range(1, 26)) + [40, 41, 45, 46, 64]:
+                parts = [rnd(rng.randrange(0, 60))]
+                for rep in range(40):
+                    kmer = rnd(19)
+                    twin = kmer if rep % 2 == 0 else "".join(comp[c] for c in reversed(kmer))
+                    if d >= 19:
+                        parts += [kmer, rnd(d - 19), twin]
+                    else:   # overlapping copies: a periodic stretch of period d holds the 19-mer again d bases later
+                        parts += [(kmer[:d] * (40 // d + 2))[:19 + d]]
+                    parts.append(rnd(rng.randrange(0, 90)))
+                s = "".join(parts)
+                assert np.array_equal(gpu.debug_minimisers(s), np.sort(oracle.minimisers(s))), (mode, d, len(s))
+        finally:
+            gpu.force_generic(0)
+
+
 def test_tie_run_crossing_a_tile_boundary_regression(small):
     """Golden regression (tests/golden/tie_tile_boundary_809.txt): a run of equal window minima crosses the 713-window
     warp tile while an EARLIER run's tracked element also sits past the tile end — only the run alive at the last window
