@@ -130,6 +130,19 @@ def cpu_baseline(wl, records, rec_bin, seconds_target=15.0, threads=0):
                      with_gzip_value=n_gz / rg["seconds"], index_build_s=round(build_s, 2), seconds=round(r["seconds"], 2)), (bases, seg_off, r)
 
 
+def parity_mismatch(g, o):
+    """None when every integer output agrees, else a description of the first differing read."""
+    for key in ("num_hashes", "counts", "unique_counts", "confidence", "call"):
+        a, b = np.asarray(g[key]), np.asarray(o[key])
+        if not np.array_equal(a, b):
+            r = int(np.argwhere(a != b)[0][0])
+            return (f"first difference in `{key}` at read {r}: gpu num_hashes={int(g['num_hashes'][r])} counts={g['counts'][r].tolist()} "
+                    f"unique={g['unique_counts'][r].tolist()} call={int(g['call'][r])} | oracle num_hashes={int(o['num_hashes'][r])} "
+                    f"counts={o['counts'][r].tolist()} unique={o['unique_counts'][r].tolist()} call={int(o['call'][r])}; "
+                    f"{int((np.asarray(g['num_hashes']) != np.asarray(o['num_hashes'])).sum())} reads differ in num_hashes")
+    return None
+
+
 def run_reference(args, wl):
     rank, local_rank, world = dist_env()
     if rank != 0:
@@ -352,13 +365,19 @@ def run_b200(args, wl):
                                  f"{info.filter_bytes / 1e6:.0f} MB"}}
     if world == 1 and not args.no_cpu_baseline:
         idx, cb, (sb, so, sr) = cpu_baseline(wl, records, rec_bin)
-        # free parity check at full index size: the oracle's own index + sample vs the GPU
+        # parity GATE at full index size: the oracle's own index + sample vs the GPU, every integer output of every read
         n = len(so) - 1
         g = gpu.classify_batch(sb, so, np.full(n, 20.0, np.float32), np.full(n, 0.3, np.float32), np.full(n, L, np.uint32))
-        cb["parity_on_sample"] = bool(np.array_equal(g["num_hashes"], sr["num_hashes"]) and np.array_equal(g["counts"], sr["counts"]) and
-                                      np.array_equal(g["unique_counts"], sr["unique_counts"]) and np.array_equal(g["call"], sr["call"]) and
-                                      np.array_equal(g["confidence"], sr["confidence"]))
+        bad = parity_mismatch(g, sr)
+        cb["parity_on_sample"] = bad is None
+        cb["parity_sample_reads"] = n
         line["cpu_baseline"] = cb
+        if bad is not None:
+            sys.stderr.write(f"bench.py: PARITY FAILURE against the oracle on the cpu_baseline sample ({n} reads): {bad}\n"
+                             "bench.py: no bench line is printed for a kernel that is not bit-exact\n")
+            sys.stderr.flush()
+            gpu.close()
+            sys.exit(3)
     emit(line)
     gpu.close()
     if dist is not None:

@@ -118,8 +118,8 @@ __device__ __forceinline__ bool neq64h(uint64_t a, uint64_t b) {
 #endif
 }
 #ifndef CG_TIE_LEAVING_ONLY
-#define CG_TIE_LEAVING_ONLY 1   // see p2_block
-#endif
+#define CG_TIE_LEAVING_ONLY 0   // see p2_block.  1 (round 1's last commit) is NOT exact on its own: a fast tile then hands no tracked
+#endif                          // position to the next one (tests/test_tile_seams.py); it needs the seam reconstruction of exact_tile.
 // Store through a 32-bit shared-space address.  A moving generic pointer costs a 64-bit add next to the address the STS uses;
 // deliberately no "memory" clobber (the window-minimum loads around it must stay free to move): the caller fences once.
 __device__ __forceinline__ void st_shared_u64(uint32_t addr, uint64_t v) { asm volatile("st.shared.u64 [%0], %1;" ::"r"(addr), "l"(v)); }
