@@ -222,14 +222,14 @@ template <int MODE, bool SMALL, bool AG = false> cudaError_t launch_count_warp(c
         if (e != cudaSuccess) return e;
         attr_done = true;
     }
-    cgk::count_kernel_v3<MODE, FAST_K, FAST_WV, SMALL, AG><<<grid, cgk::WARPS3 * 32, C::SMEM, h->stream>>>(P);
+    cgk::count_kernel_v3<MODE, FAST_K, FAST_WV, SMALL, AG><<<grid, cgk::V3Shape<AG>::WARPS * 32, C::SMEM, h->stream>>>(P);
     return cudaGetLastError();
 }
 template <int MODE, bool SMALL, bool AG = false> int occupancy_warp() {
     using C = cgk::V3Cfg<FAST_K, FAST_WV, SMALL, AG>;
     int n = 0;
     cudaFuncSetAttribute(cgk::count_kernel_v3<MODE, FAST_K, FAST_WV, SMALL, AG>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(C::SMEM));
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, cgk::count_kernel_v3<MODE, FAST_K, FAST_WV, SMALL, AG>, cgk::WARPS3 * 32, C::SMEM);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, cgk::count_kernel_v3<MODE, FAST_K, FAST_WV, SMALL, AG>, cgk::V3Shape<AG>::WARPS * 32, C::SMEM);
     return n;
 }
 template <int MODE> int occupancy_mode() {
@@ -253,7 +253,9 @@ int launch_count(cg_handle *h, const cgk::CountParams &P) {
         cgk::CountParams Q = P;
         const bool dispatch = Q.seg_len == nullptr;          // index-build chunks are all handled by the warp kernel
         Q.long_read_min = dispatch ? LONG_READ_MIN : 0;
-        const int wgrid = int(std::min<uint64_t>(uint64_t(h->sm_count) * (Q.async_gather && h->mode == 0 ? h->warp_grid_per_sm_ag : h->warp_grid_per_sm), (uint64_t(P.n_reads) + cgk::WARPS3 - 1) / cgk::WARPS3));
+        const bool use_ag = Q.async_gather && h->mode == 0;
+        const uint64_t wpc = use_ag ? cgk::V3Shape<true>::WARPS : cgk::V3Shape<false>::WARPS;   // warps (= reads in flight) per CTA
+        const int wgrid = int(std::min<uint64_t>(uint64_t(h->sm_count) * (use_ag ? h->warp_grid_per_sm_ag : h->warp_grid_per_sm), (uint64_t(P.n_reads) + wpc - 1) / wpc));
         const bool small = h->bins <= 4;
         switch (h->mode) {
             case 0:   // narrow rows: the deferred gathers fly as cp.async when the filter is beyond L2 (count_kernel_v3.cuh)

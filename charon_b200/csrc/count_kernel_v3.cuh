@@ -31,7 +31,17 @@ namespace cgk {
 #ifndef CG_V3_MINB
 #define CG_V3_MINB 3
 #endif
-constexpr int WARPS3 = CG_V3_WARPS;    // warps per CTA (independent of each other)
+#ifndef CG_V3_WARPS_AG
+#define CG_V3_WARPS_AG 12   // the cp.async-carrier kernel (filter beyond L2) runs best as ONE 12-warp CTA per SM (measured: 4x3 6.25 ms,
+#endif                      // 12x1 5.95 ms human-scale; the register-carrier kernel the other way round: 4.70 vs 4.81 ms bacterial)
+#ifndef CG_V3_MINB_AG
+#define CG_V3_MINB_AG 1
+#endif
+// warps per CTA (independent of each other) and resident CTAs per SM, per gather carrier
+template <bool AG> struct V3Shape {
+    static constexpr int WARPS = AG ? CG_V3_WARPS_AG : CG_V3_WARPS;
+    static constexpr int MINB = AG ? CG_V3_MINB_AG : CG_V3_MINB;
+};
 #ifndef CG_V3_WLIST_CAP
 #define CG_V3_WLIST_CAP 256
 #endif
@@ -53,7 +63,7 @@ template <int KK, int WW, bool SMALL, bool AG = false> struct V3Cfg {
     static constexpr int PRIV_GUARD = WW + 1 - PRIV_CAP > 0 ? WW + 1 - PRIV_CAP : 0;
     static constexpr size_t WARP_BYTES = size_t(NK) * 8 + (size_t(32) * PRIV_CAP + PRIV_GUARD) * 8 + size_t(WLIST_CAP) * 8 + size_t(NCNT) * 8 + 32 +
                                          size_t(NCNT) * 4 * 2 + CODES + RAW + GQ;
-    static constexpr size_t SMEM = 512 + WARPS3 * WARP_BYTES;
+    static constexpr size_t SMEM = 512 + V3Shape<AG>::WARPS * WARP_BYTES;
     static_assert(((size_t(32) * PRIV_CAP + PRIV_GUARD) * 8) % 16 == 0 && CODES % 16 == 0 && WARP_BYTES % 16 == 0,
                   "the staging vectors behind the slots need 16-byte alignment");
 };
@@ -62,13 +72,15 @@ template <int MODE, int KK, int WW, bool SMALL, bool AG = false>
 #ifdef CG_V3_MAXNREG
 __global__ void __maxnreg__(CG_V3_MAXNREG)
 #else
-__global__ void __launch_bounds__(WARPS3 * 32, CG_V3_MINB)
+__global__ void __launch_bounds__(V3Shape<AG>::WARPS * 32, V3Shape<AG>::MINB)
 #endif
 count_kernel_v3(const __grid_constant__ CountParams P) {
     using C2 = V2Cfg<KK, WW>;
     using C = V3Cfg<KK, WW, SMALL, AG && MODE == 0>;
     constexpr int NW = ModeTraits<MODE>::NW;
     constexpr int KL = C2::KL, KH = C2::KH;
+    constexpr int WARPS3 = V3Shape<AG>::WARPS;
+    static_assert(!AG || MODE == 0, "the cp.async carrier only exists for narrow rows");
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
     Smem2 S;
@@ -94,7 +106,13 @@ count_kernel_v3(const __grid_constant__ CountParams P) {
 
     const bool small_bins = SMALL;
     const uint64_t seed = P.seed;
-    const uint64_t pol_filter = l2_policy_evict_last(), pol_stream = l2_policy_evict_first();
+    // filter rows: sticky in L2 while the filter can live there; a filter beyond L2 (AG) gains nothing from stickiness
+#ifndef CG_V3_AG_POLICY
+#define CG_V3_AG_POLICY 1   // measured on the 858 MB filter: evict_last 5.93 ms, evict_first 5.83, evict_normal / unchanged 5.93-5.94
+#endif
+    const uint64_t pol_filter = !AG || CG_V3_AG_POLICY == 0 ? l2_policy_evict_last()
+                                : (CG_V3_AG_POLICY == 1 ? l2_policy_evict_first() : (CG_V3_AG_POLICY == 2 ? l2_policy_evict_normal() : l2_policy_evict_unchanged()));
+    const uint64_t pol_stream = l2_policy_evict_first();
     for (uint32_t i = tid; i < 256; i += WARPS3 * 32) { S.lut[i] = base_code(i); S.b2c[i] = P.bin_to_cat[i]; }
     __syncthreads();   // the only CTA-wide barrier
 
@@ -190,48 +208,98 @@ count_kernel_v3(const __grid_constant__ CountParams P) {
             // alone made the register carrier 20-50 % slower, so the two structures are kept apart at compile time.  (Measured and dropped: 4-byte cp.async.ca, prefetch.global.L2.)
             constexpr int DQ = (MODE == 0) ? CG_V3_DQ : 0;
             constexpr int DQA = (MODE == 0) ? CG_V3_DQA : 0;
-            constexpr int DQM = DQ > DQA ? DQ : DQA;
-            uint32_t dq_w[DQ ? DQ : 1][3], dq_sh[DQM ? DQM : 1];
+            constexpr bool ag = AG && (MODE == 0);
+            uint32_t dq_w[(DQ && !ag) ? DQ : 1][3], dq_sh[(DQ && !ag) ? DQ : 1];
             uint32_t ndq = 0;
             const bool can_defer = DQ && P.hash_funs == 3 && P.n_parts == 0;
-            constexpr bool ag = AG && (MODE == 0);
-            auto dq_finish = [&](bool bases_group_behind) {
-                if (DQ) {
+            auto dq_finish = [&]() {   // register carrier: consume the rows fetched at the end of the previous tile
+                if (DQ && !ag) {
                     const uint32_t rb = 1u << P.row_shift;
-                    const uint32_t msk = rb >= 32 ? 0xFFFFFFFFu : ((1u << rb) - 1u);
-                    if (ag) {
-                        if (ndq) {
-                            if (bases_group_behind) asm volatile("cp.async.wait_group 1;" ::: "memory");
-                            else asm volatile("cp.async.wait_group 0;" ::: "memory");
+                    const uint32_t row_msk = rb >= 32 ? 0xFFFFFFFFu : ((1u << rb) - 1u);
+#pragma unroll
+                    for (int g = 0; g < DQ; ++g)
+                        if (g < int(ndq)) {
+                            Mask<NW> m;
+#pragma unroll
+                            for (int j = 1; j < NW; ++j) m.w[j] = 0;
+                            m.w[0] = ((dq_w[g][0] >> (dq_sh[g] & 31u)) & (dq_w[g][1] >> ((dq_sh[g] >> 5) & 31u)) & (dq_w[g][2] >> ((dq_sh[g] >> 10) & 31u))) & row_msk;
+                            T.add(m, bm, small_bins, do_tot, do_unq, S);
                         }
-#pragma unroll
-                        for (int g = 0; g < DQA; ++g)
-                            if (g < int(ndq)) {
-                                const uint32_t sh = dq_sh[g];
-                                uint32_t w[3];
-#pragma unroll
-                                for (int i = 0; i < 3; ++i)
-                                    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w[i]) : "r"(gq_s + uint32_t(g * 3 + i) * 512u + (((sh >> (15 + 2 * i)) & 3u) << 2)) : "memory");
-                                Mask<NW> m;
-#pragma unroll
-                                for (int j = 1; j < NW; ++j) m.w[j] = 0;
-                                m.w[0] = ((w[0] >> (sh & 31u)) & (w[1] >> ((sh >> 5) & 31u)) & (w[2] >> ((sh >> 10) & 31u))) & msk;
-                                T.add(m, bm, small_bins, do_tot, do_unq, S);
-                            }
-                    } else {
-#pragma unroll
-                        for (int g = 0; g < DQ; ++g)
-                            if (g < int(ndq)) {
-                                Mask<NW> m;
-#pragma unroll
-                                for (int j = 1; j < NW; ++j) m.w[j] = 0;
-                                m.w[0] = ((dq_w[g][0] >> (dq_sh[g] & 31u)) & (dq_w[g][1] >> ((dq_sh[g] >> 5) & 31u)) & (dq_w[g][2] >> ((dq_sh[g] >> 10) & 31u))) & msk;
-                                T.add(m, bm, small_bins, do_tot, do_unq, S);
-                            }
-                    }
                 }
                 ndq = 0;
             };
+            // cp.async carrier (AG): a TWO-STAGE pipeline with early exit.  bulk_contains is the AND of the three hash rows
+            // (include/index.hpp:110-112 via seqan3), so a minimiser whose first row holds no bin at all cannot be in any bin:
+            // rows 1 and 2 are only fetched for the lanes whose row 0 came back non-zero.  On a filter beyond L2 every row
+            // is a DRAM line, and with k-mers broken by read errors about half of all minimisers stop after one line.
+            //   end of tile t   : cohort A(t) = the first DQA full groups: row 0 -> cp.async into slot (g, 0)           [stage 0]
+            //   end of tile t+1 : A(t): m0 = row-0 bits; lanes with m0 != 0 fetch rows 1, 2 into slots (g, 1), (g, 2)  [stage 1]
+            //   end of tile t+2 : A(t): mask = m0 & row 1 & row 2 -> tallies
+            // The values of a stage-0 cohort stay in the ring (behind its head) until its rows 1, 2 have been derived.
+            uint32_t s0_n = 0, s1_n = 0, s0_base = 0, s0_span = 0;         // warp-uniform: groups per stage; ring index of the stage-0 cohort's first value and how far the head has moved past it
+            uint32_t s0_sh[DQA ? DQA : 1], s1_sh[DQA ? DQA : 1], s1_m0[DQA ? DQA : 1];
+            auto ag_step = [&](bool bases_group_behind, uint32_t new_groups) {
+                if (ag) {
+                    const uint32_t rb = 1u << P.row_shift;
+                    const uint32_t row_msk = rb >= 32 ? 0xFFFFFFFFu : ((1u << rb) - 1u);
+                    if (s0_n | s1_n) {
+                        if (bases_group_behind) asm volatile("cp.async.wait_group 1;" ::: "memory");
+                        else asm volatile("cp.async.wait_group 0;" ::: "memory");
+                    }
+                    // stage 1 -> done
+#pragma unroll
+                    for (int g = 0; g < DQA; ++g)
+                        if (g < int(s1_n) && s1_m0[g]) {
+                            const uint32_t sh = s1_sh[g];
+                            uint32_t w1, w2;
+                            asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w1) : "r"(gq_s + uint32_t(g * 3 + 1) * 512u + (((sh >> 10) & 3u) << 2)) : "memory");
+                            asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w2) : "r"(gq_s + uint32_t(g * 3 + 2) * 512u + (((sh >> 12) & 3u) << 2)) : "memory");
+                            Mask<NW> m;
+#pragma unroll
+                            for (int j = 1; j < NW; ++j) m.w[j] = 0;
+                            m.w[0] = s1_m0[g] & (w1 >> (sh & 31u)) & (w2 >> ((sh >> 5) & 31u));
+                            if (m.w[0]) T.add(m, bm, small_bins, do_tot, do_unq, S);
+                        }
+                    // stage 0 -> stage 1
+#pragma unroll
+                    for (int g = 0; g < DQA; ++g)
+                        if (g < int(s0_n)) {
+                            uint32_t w0;
+                            asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w0) : "r"(gq_s + uint32_t(g * 3) * 512u + (((s0_sh[g] >> 5) & 3u) << 2)) : "memory");
+                            const uint32_t m0 = (w0 >> (s0_sh[g] & 31u)) & row_msk;
+                            uint32_t sh = 0;
+                            if (m0) {
+                                const uint64_t value = ring[(s0_base + uint32_t(g) * 32u + lane) & uint32_t(WLIST_CAP - 1)];
+#pragma unroll
+                                for (int i = 1; i < 3; ++i) {
+                                    const uint32_t row = ibf_row32(value, c_ibf_seeds[i], P.hash_shift, uint32_t(P.bin_size));
+                                    const uint32_t word = row >> (5u - P.row_shift);
+                                    asm volatile("cp.async.cg.shared.global.L2::cache_hint [%0], [%1], 16, %2;" ::"r"(gq_s + uint32_t(g * 3 + i) * 512u),
+                                                 "l"(reinterpret_cast<const uint32_t *>(P.filter) + (word & ~3u)), "l"(pol_filter)
+                                                 : "memory");
+                                    sh |= (((row << P.row_shift) & 31u) << (5 * (i - 1))) | ((word & 3u) << (10 + 2 * (i - 1)));
+                                }
+                            }
+                            s1_sh[g] = sh; s1_m0[g] = m0;
+                        }
+                    s1_n = s0_n;
+                    // new cohort -> stage 0
+#pragma unroll
+                    for (int g = 0; g < DQA; ++g)
+                        if (uint32_t(g) < new_groups) {
+                            const uint64_t value = LI(g * 32 + lane);
+                            const uint32_t row = ibf_row32(value, c_ibf_seeds[0], P.hash_shift, uint32_t(P.bin_size));
+                            const uint32_t word = row >> (5u - P.row_shift);
+                            asm volatile("cp.async.cg.shared.global.L2::cache_hint [%0], [%1], 16, %2;" ::"r"(gq_s + uint32_t(g * 3) * 512u),
+                                         "l"(reinterpret_cast<const uint32_t *>(P.filter) + (word & ~3u)), "l"(pol_filter)
+                                         : "memory");
+                            s0_sh[g] = ((row << P.row_shift) & 31u) | ((word & 3u) << 5);
+                        }
+                    s0_n = new_groups;
+                    s0_base = qh;
+                }
+            };
+            (void)s0_span;
             for (uint32_t seg = seg0; seg < seg1; ++seg) {
                 const uint64_t sbase = P.seg_off[seg];
                 const uint64_t slen = P.seg_len ? P.seg_len[seg] : P.seg_off[seg + 1] - sbase;
@@ -417,7 +485,7 @@ count_kernel_v3(const __grid_constant__ CountParams P) {
 #pragma unroll
                     for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, inc, o); if (lane >= uint32_t(o)) inc += t; }
                     uint32_t nl = __shfl_sync(0xFFFFFFFFu, inc, 31);
-                    const bool redo = __any_sync(0xFFFFFFFFu, tie) || pend + nl > WLIST_CAP;
+                    const bool redo = __any_sync(0xFFFFFFFFu, tie) || s0_span + pend + nl > WLIST_CAP;   // the ring also holds the stage-0 cohort's values
                     if (!redo) {
                         uint32_t dst = pend + inc - cnt;
                         for (uint32_t q = 0; q < cnt; ++q, ++dst) LI(dst) = pslot0[q];
@@ -450,27 +518,13 @@ count_kernel_v3(const __grid_constant__ CountParams P) {
                         const uint32_t fullg = (pend + nl) & ~31u;
                         uint32_t first_now = 0;   // groups below this index go through the deferred queue
                         if (can_defer) {
-                            dq_finish(true);      // issued one tile ago; this tile's bases group was committed after them
                             const uint32_t ngroups = fullg >> 5;
                             if (ag) {
-#pragma unroll
-                                for (int g = 0; g < DQA; ++g)
-                                    if (uint32_t(g) < ngroups) {
-                                        const uint64_t value = LI(g * 32 + lane);
-                                        uint32_t sh = 0;
-#pragma unroll
-                                        for (int i = 0; i < 3; ++i) {
-                                            const uint32_t row = ibf_row32(value, c_ibf_seeds[i], P.hash_shift, uint32_t(P.bin_size));
-                                            const uint32_t word = row >> (5u - P.row_shift);
-                                            asm volatile("cp.async.cg.shared.global.L2::cache_hint [%0], [%1], 16, %2;" ::"r"(gq_s + uint32_t(g * 3 + i) * 512u),
-                                                         "l"(reinterpret_cast<const uint32_t *>(P.filter) + (word & ~3u)), "l"(pol_filter)
-                                                         : "memory");
-                                            sh |= (((row << P.row_shift) & 31u) << (5 * i)) | ((word & 3u) << (15 + 2 * i));
-                                        }
-                                        dq_sh[g] = sh;
-                                    }
                                 ndq = ngroups < uint32_t(DQA) ? ngroups : uint32_t(DQA);
+                                ag_step(true, ndq);   // this tile's bases group was committed after the gathers that are consumed now
+                                s0_span = ndq ? fullg : 0u;
                             } else {
+                                dq_finish();          // issued one tile ago
 #pragma unroll
                                 for (int g = 0; g < DQ; ++g)
                                     if (uint32_t(g) < ngroups) {
@@ -501,7 +555,13 @@ count_kernel_v3(const __grid_constant__ CountParams P) {
                     first = false;
                 }  // tiles
             }      // segments
-            dq_finish(false);
+            if (ag) {              // drain both stages (each step commits its own, possibly empty, group)
+                if (can_defer) {
+                    ag_step(false, 0);
+                    asm volatile("cp.async.commit_group;" ::: "memory");
+                    ag_step(false, 0);
+                }
+            } else dq_finish();
             if (pend) {   // flush what is still waiting at the end of this pass
                 __syncwarp();
                 for (uint32_t i = lane; i < pend; i += 32) {
