@@ -4,4 +4,5 @@ csrc/   hand-written sm_100a kernels + the C-ABI (include/charon_gpu.h) -> libch
 host/   C++14 host program: index loader, FASTA/Q ingest, pre-filters, TSV writer, CLI
 api.py  ctypes mirror used by the Python tests and bench.py
 """
-from .api import GpuClassifier, DehostOptions, ClassifyOptions, CharonGpuError, load_library, LIB_PATH  # noqa: F401
+from .api import (GpuClassifier, DehostOptions, ClassifyOptions, CharonGpuError, load_library, LIB_PATH, PackedBatch, pack_batch,  # noqa: F401
+                  BASES_ASCII, BASES_RANK4, BASES_2BIT)

@@ -37,7 +37,11 @@ class Thresholds(C.Structure):
 
 
 class Batch(C.Structure):
-    _fields_ = [("bases", vp), ("seg_off", vp), ("read_seg", vp), ("n_reads", u32), ("n_segs", u32)]
+    _fields_ = [("bases", vp), ("seg_off", vp), ("read_seg", vp), ("n_reads", u32), ("n_segs", u32),
+                ("bases_format", i32), ("seg_len", vp), ("exc_pos", vp), ("n_exc", u64)]
+
+
+BASES_ASCII, BASES_RANK4, BASES_2BIT = 0, 1, 2
 
 
 class CountsOut(C.Structure):
@@ -62,7 +66,7 @@ class Info(C.Structure):
 EXPORTS = ["cg_create", "cg_build_index", "cg_destroy", "cg_last_error", "cg_set_stream", "cg_sync", "cg_set_model", "cg_count_batch", "cg_eval_batch",
            "cg_classify_batch", "cg_stage_batch", "cg_run_staged", "cg_fetch_staged", "cg_get_info", "cg_host_alloc", "cg_host_free", "cg_timer_start", "cg_timer_stop", "cg_debug_minimisers",
            "cg_debug_query", "cg_debug_dump_filter", "cg_debug_force_generic", "cg_create_partitioned", "cg_partition_from_replicated",
-           "cg_partition_export", "cg_partition_attach_ipc", "cg_partition_attach_peer", "cg_bench_gather", "cg_submit_batch", "cg_wait_batch", "cg_export_sd_vector", "cg_select_slot", "cg_set_host_pack", "cg_pack_bases"]
+           "cg_partition_export", "cg_partition_attach_ipc", "cg_partition_attach_peer", "cg_bench_gather", "cg_submit_batch", "cg_wait_batch", "cg_export_sd_vector", "cg_select_slot", "cg_set_host_pack", "cg_pack_bases", "cg_pack_bases_2bit"]
 
 _lib = None
 
@@ -89,6 +93,7 @@ def load_library():
     L.cg_select_slot.argtypes = [vp, i32]
     L.cg_set_host_pack.argtypes = [vp, i32, i32]
     L.cg_pack_bases.argtypes = [vp, u64, vp]
+    L.cg_pack_bases_2bit.argtypes = [vp, u64, vp, u64, vp, u64, P(u64)]
     L.cg_export_sd_vector.argtypes = [vp, P(u64), P(C.c_uint8), P(u64), P(u64), vp, vp]
     L.cg_bench_gather.argtypes = [vp, u64, i32, i32, P(f32)]
     L.cg_destroy.argtypes = [vp]; L.cg_destroy.restype = None
@@ -156,6 +161,56 @@ def pack_bases(bases) -> np.ndarray:
     if rc:
         raise RuntimeError(f"cg_pack_bases failed ({rc})")
     return out
+
+
+class PackedBatch:
+    """A batch whose bases are already in one of the packed transports (what a parser written for this library emits).
+    `bases` packed bytes, `seg_off` / `seg_len` in bases (segments may be padded apart), `exc_pos` for BASES_2BIT."""
+
+    def __init__(self, fmt, bases, seg_off, seg_len=None, exc_pos=None, read_seg=None):
+        self.fmt, self.bases, self.seg_off, self.seg_len, self.exc_pos, self.read_seg = fmt, bases, seg_off, seg_len, exc_pos, read_seg
+
+
+def pack_batch(bases, seg_off, fmt=BASES_2BIT, align=64, read_seg=None, out=None) -> PackedBatch:
+    """Pack an ASCII batch (concatenated bases + offsets) read by read into `fmt`, every segment starting on a multiple of
+    `align` bases — what host/fastx.hpp does while it parses.  `out`: optional preallocated uint8 buffer (e.g. pinned)."""
+    L = load_library()
+    b = np.ascontiguousarray(bases, np.uint8)
+    so = np.ascontiguousarray(seg_off, np.uint64)
+    n = len(so) - 1
+    lens = np.diff(so).astype(np.uint64)
+    per = 4 if fmt == BASES_2BIT else 2
+    assert fmt in (BASES_2BIT, BASES_RANK4) and align % per == 0
+    padded = (lens + np.uint64(align - 1)) // np.uint64(align) * np.uint64(align)
+    new_off = np.zeros(n + 1, np.uint64)
+    np.cumsum(padded, out=new_off[1:])
+    total = int(new_off[-1])
+    nbytes = (total + per - 1) // per + 16
+    buf = out if out is not None else np.zeros(nbytes, np.uint8)
+    assert buf.size >= nbytes
+    exc = np.zeros(max(16, total // 64), np.uint64)
+    n_exc = 0
+    k = u64(0)
+    for s in range(n):
+        lo, ln, dst = int(so[s]), int(lens[s]), int(new_off[s])
+        if ln == 0:
+            continue
+        src = b[lo:lo + ln]
+        if fmt == BASES_2BIT:
+            while True:
+                cap = exc.size - n_exc
+                rc = L.cg_pack_bases_2bit(src.ctypes.data, ln, buf.ctypes.data + dst // 4, dst, exc.ctypes.data + 8 * n_exc, cap, C.byref(k))
+                if rc:
+                    raise CharonGpuError(f"cg_pack_bases_2bit failed ({rc}): {L.cg_last_error(None).decode()}")
+                if k.value <= cap:
+                    break
+                exc = np.concatenate([exc, np.zeros(max(exc.size, int(k.value)), np.uint64)])
+            n_exc += int(k.value)
+        else:
+            rc = L.cg_pack_bases(src.ctypes.data, ln, buf.ctypes.data + dst // 2)
+            if rc:
+                raise CharonGpuError(f"cg_pack_bases failed ({rc})")
+    return PackedBatch(fmt, buf, new_off, lens, exc[:n_exc].copy() if fmt == BASES_2BIT else None, read_seg)
 
 
 def _ptr(a):
@@ -312,6 +367,16 @@ class GpuClassifier:
 
     # ---- batches --------------------------------------------------------------------------------------------
     def _batch(self, bases, seg_off, read_seg):
+        if isinstance(bases, PackedBatch):
+            pb = bases
+            so = np.ascontiguousarray(pb.seg_off, np.uint64)
+            sl = np.ascontiguousarray(pb.seg_len, np.uint64) if pb.seg_len is not None else None
+            ex = np.ascontiguousarray(pb.exc_pos, np.uint64) if pb.exc_pos is not None and len(pb.exc_pos) else None
+            rs = np.ascontiguousarray(pb.read_seg if pb.read_seg is not None else read_seg, dtype=np.uint32) if (pb.read_seg is not None or read_seg is not None) else None
+            n_segs = len(so) - 1
+            n_reads = len(rs) - 1 if rs is not None else n_segs
+            b = Batch(pb.bases.ctypes.data, so.ctypes.data, _ptr(rs), n_reads, n_segs, pb.fmt, _ptr(sl), _ptr(ex), len(ex) if ex is not None else 0)
+            return b, (pb.bases, so, sl, ex, rs), n_reads
         bases = np.ascontiguousarray(bases, dtype=np.uint8)
         seg_off = np.ascontiguousarray(seg_off, dtype=np.uint64)
         rs = np.ascontiguousarray(read_seg, dtype=np.uint32) if read_seg is not None else None

@@ -79,12 +79,16 @@ struct cg_handle {
     cg_thresholds thr{};
     // batch buffers
     DevBuf bases, seg_off, read_seg, num_hashes, counts, unique, prob, call, conf, mq, cr, len, counter, dbg, dbgn;
+    DevBuf seg_len, exc_pos, exc_seg_off, unpack_src;   // optional segment lengths; two-bit transport: exception list + per-segment CSR; packed input of the generic kernel
     uint32_t staged_reads = 0, staged_segs = 0;
     uint64_t staged_bases = 0;
     bool staged_has_read_seg = false, staged_has_scalars = false;
     // packed transport (host_pack.hpp): the staged bases are 4-bit ranks; pinned staging buffer of the active slot and the
     // event that says its last chunk has been copied out
-    bool staged_packed = false;
+    int staged_format = 0;        // enum cg_bases_format of the bases as they sit in `bases` (what the kernels decode)
+    bool staged_has_seg_len = false;
+    uint64_t staged_n_exc = 0;
+    bool staged_packed = false;   // staged_format == CG_BASES_RANK4 produced by the library's own packer
     struct PackStage { void *p = nullptr; size_t cap = 0; cudaEvent_t done = nullptr; bool armed = false; } pack;
     int async_gather_mode = -1;   // -1: by filter size, 0 / 1: forced (env CHARON_ASYNC_GATHER, test hook)
     int host_pack_mode = -1;      // -1: automatic (thread pool of at least 8), 0: never, 1: whenever the (19, 41) kernels apply
@@ -99,7 +103,8 @@ struct cg_handle {
     struct Parked {
         cudaStream_t stream = nullptr;
         cudaEvent_t ev[8] = {};
-        DevBuf bases, seg_off, read_seg, num_hashes, counts, unique, prob, call, conf, mq, cr, len, counter;
+        DevBuf bases, seg_off, read_seg, num_hashes, counts, unique, prob, call, conf, mq, cr, len, counter, seg_len, exc_pos, exc_seg_off, unpack_src;
+        int staged_format = 0; bool staged_has_seg_len = false; uint64_t staged_n_exc = 0;
         uint32_t staged_reads = 0, staged_segs = 0;
         uint64_t staged_bases = 0, staged_max_read_len = 0;
         bool staged_has_read_seg = false, staged_has_scalars = false, staged_packed = false;
@@ -122,6 +127,8 @@ struct cg_handle {
         std::swap(staged_bases, parked.staged_bases); std::swap(staged_max_read_len, parked.staged_max_read_len);
         std::swap(staged_has_read_seg, parked.staged_has_read_seg); std::swap(staged_has_scalars, parked.staged_has_scalars);
         std::swap(staged_packed, parked.staged_packed); std::swap(pack, parked.pack);
+        std::swap(seg_len, parked.seg_len); std::swap(exc_pos, parked.exc_pos); std::swap(exc_seg_off, parked.exc_seg_off); std::swap(unpack_src, parked.unpack_src);
+        std::swap(staged_format, parked.staged_format); std::swap(staged_has_seg_len, parked.staged_has_seg_len); std::swap(staged_n_exc, parked.staged_n_exc);
         std::swap(active_pending, parked.pending);
         std::swap(act_co, parked.co); std::swap(act_ca, parked.ca); std::swap(act_has_co, parked.has_co); std::swap(act_has_ca, parked.has_ca);
         active_slot ^= 1;
@@ -171,10 +178,11 @@ cgk::CountParams make_params(cg_handle *h) {
     P.bin_to_cat = h->d_bin_to_cat;
     P.num_hashes = h->num_hashes.as<uint32_t>(); P.counts = h->counts.as<uint32_t>(); P.unique_counts = h->unique.as<uint32_t>();
     P.work_counter = h->counter.as<uint32_t>();
-    P.seg_len = nullptr;
+    P.seg_len = h->staged_has_seg_len ? h->seg_len.as<uint64_t>() : nullptr;
     P.long_read_min = 0; P.long_only = 0;
     P.dbg_out = nullptr; P.dbg_cap = 0; P.dbg_n = nullptr;
-    P.n_parts = h->n_parts; P.my_part = h->my_part; P.rows_per_part = h->rows_per_part; P.packed = h->staged_packed ? 1 : 0;
+    P.n_parts = h->n_parts; P.my_part = h->my_part; P.rows_per_part = h->rows_per_part; P.packed = uint32_t(h->staged_format);
+    P.n_exc = h->staged_n_exc; P.exc_pos = h->exc_pos.as<unsigned long long>(); P.exc_seg_off = h->exc_seg_off.as<uint32_t>();
     P.async_gather = h->async_gather_mode < 0 ? (h->filter_bytes > ASYNC_GATHER_MIN_FILTER ? 1 : 0) : uint32_t(h->async_gather_mode);
     if (h->hash_funs != 3 || h->n_parts || h->mode != 0) P.async_gather = 0;   // the cp.async carrier exists for the deferred-gather case only
     for (int i = 0; i < CG_MAX_PARTS; ++i) P.part_base[i] = h->part_base[i];
@@ -214,23 +222,31 @@ template <int MODE> int occupancy_fast() {
 }
 // warp-per-read kernel (count_kernel_v3): SMALL = at most 4 bins (register tallies, no per-warp counter arrays)
 constexpr unsigned long long LONG_READ_MIN = 65536;   // reads at least this long go to the CTA-per-read kernel
-template <int MODE, bool SMALL, bool AG = false> cudaError_t launch_count_warp(cg_handle *h, const cgk::CountParams &P, int grid) {
+template <int MODE, bool SMALL, bool AG, int FMT> cudaError_t launch_count_warp_fmt(cg_handle *h, const cgk::CountParams &P, int grid) {
     using C = cgk::V3Cfg<FAST_K, FAST_WV, SMALL, AG>;
     static bool attr_done = false;
     if (!attr_done) {
-        cudaError_t e = cudaFuncSetAttribute(cgk::count_kernel_v3<MODE, FAST_K, FAST_WV, SMALL, AG>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(C::SMEM));
+        cudaError_t e = cudaFuncSetAttribute(cgk::count_kernel_v3<MODE, FAST_K, FAST_WV, SMALL, AG, FMT>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(C::SMEM));
         if (e != cudaSuccess) return e;
         attr_done = true;
     }
-    cgk::count_kernel_v3<MODE, FAST_K, FAST_WV, SMALL, AG><<<grid, cgk::V3Shape<AG>::WARPS * 32, C::SMEM, h->stream>>>(P);
+    cgk::count_kernel_v3<MODE, FAST_K, FAST_WV, SMALL, AG, FMT><<<grid, cgk::V3Shape<AG, SMALL>::WARPS * 32, C::SMEM, h->stream>>>(P);
     return cudaGetLastError();
 }
-template <int MODE, bool SMALL, bool AG = false> int occupancy_warp() {
+template <int MODE, bool SMALL, bool AG = false> cudaError_t launch_count_warp(cg_handle *h, const cgk::CountParams &P, int grid) {
+    return P.packed == CG_BASES_2BIT ? launch_count_warp_fmt<MODE, SMALL, AG, CG_BASES_2BIT>(h, P, grid) : launch_count_warp_fmt<MODE, SMALL, AG, CG_BASES_ASCII>(h, P, grid);
+}
+template <int MODE, bool SMALL, bool AG = false> int occupancy_warp() {   // the same for both base formats (same registers to within ptxas' whim: take the lower)
     using C = cgk::V3Cfg<FAST_K, FAST_WV, SMALL, AG>;
-    int n = 0;
-    cudaFuncSetAttribute(cgk::count_kernel_v3<MODE, FAST_K, FAST_WV, SMALL, AG>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(C::SMEM));
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, cgk::count_kernel_v3<MODE, FAST_K, FAST_WV, SMALL, AG>, cgk::V3Shape<AG>::WARPS * 32, C::SMEM);
-    return n;
+    int n0 = 0, n2 = 0;
+    if (cudaFuncSetAttribute(cgk::count_kernel_v3<MODE, FAST_K, FAST_WV, SMALL, AG, CG_BASES_ASCII>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(C::SMEM)) != cudaSuccess ||
+        cudaFuncSetAttribute(cgk::count_kernel_v3<MODE, FAST_K, FAST_WV, SMALL, AG, CG_BASES_2BIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(C::SMEM)) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n0, cgk::count_kernel_v3<MODE, FAST_K, FAST_WV, SMALL, AG, CG_BASES_ASCII>, cgk::V3Shape<AG, SMALL>::WARPS * 32, C::SMEM);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n2, cgk::count_kernel_v3<MODE, FAST_K, FAST_WV, SMALL, AG, CG_BASES_2BIT>, cgk::V3Shape<AG, SMALL>::WARPS * 32, C::SMEM);
+    return std::min(n0, n2);
 }
 template <int MODE> int occupancy_mode() {
     int n = 0;
@@ -251,12 +267,12 @@ int launch_count(cg_handle *h, const cgk::CountParams &P) {
     if (use_fast(h) && !h->force_cta) {
         // warp-per-read kernel for everything shorter than LONG_READ_MIN, then (only if needed) the CTA-per-read kernel
         cgk::CountParams Q = P;
-        const bool dispatch = Q.seg_len == nullptr;          // index-build chunks are all handled by the warp kernel
+        const bool dispatch = Q.filter != nullptr;           // index-build chunks (capture-only launch) are all handled by the warp kernel
         Q.long_read_min = dispatch ? LONG_READ_MIN : 0;
         const bool use_ag = Q.async_gather && h->mode == 0;
-        const uint64_t wpc = use_ag ? cgk::V3Shape<true>::WARPS : cgk::V3Shape<false>::WARPS;   // warps (= reads in flight) per CTA
-        const int wgrid = int(std::min<uint64_t>(uint64_t(h->sm_count) * (use_ag ? h->warp_grid_per_sm_ag : h->warp_grid_per_sm), (uint64_t(P.n_reads) + wpc - 1) / wpc));
         const bool small = h->bins <= 4;
+        const uint64_t wpc = use_ag ? (small ? cgk::V3Shape<true, true>::WARPS : cgk::V3Shape<true, false>::WARPS) : cgk::V3Shape<false>::WARPS;   // warps (= reads in flight) per CTA
+        const int wgrid = int(std::min<uint64_t>(uint64_t(h->sm_count) * (use_ag ? h->warp_grid_per_sm_ag : h->warp_grid_per_sm), (uint64_t(P.n_reads) + wpc - 1) / wpc));
         switch (h->mode) {
             case 0:   // narrow rows: the deferred gathers fly as cp.async when the filter is beyond L2 (count_kernel_v3.cuh)
                 if (Q.async_gather) e = small ? launch_count_warp<0, true, true>(h, Q, wgrid) : launch_count_warp<0, false, true>(h, Q, wgrid);
@@ -344,7 +360,33 @@ int validate_batch(cg_handle *h, const cg_batch *b) {
     if (!b || (!b->seg_off && b->n_segs) || (!b->bases && b->n_segs && b->seg_off[b->n_segs] > 0)) return fail(h, CG_ERR_ARG, "null batch pointers");
     if (!b->read_seg && b->n_segs != b->n_reads) return fail(h, CG_ERR_ARG, "read_seg is NULL but n_segs != n_reads");
     if (b->read_seg && (b->read_seg[0] != 0 || b->read_seg[b->n_reads] != b->n_segs)) return fail(h, CG_ERR_ARG, "read_seg must span [0, n_segs]");
+    if (b->bases_format < CG_BASES_ASCII || b->bases_format > CG_BASES_2BIT) return fail(h, CG_ERR_ARG, "bases_format %d unknown", b->bases_format);
+    if (b->n_exc && (b->bases_format != CG_BASES_2BIT || !b->exc_pos)) return fail(h, CG_ERR_ARG, "exc_pos / n_exc only go with CG_BASES_2BIT");
+    // one pass over the offsets: a non-monotone table would make segment lengths wrap around and the kernels read out of bounds
+    if (b->n_segs && b->seg_off[0] != 0) return fail(h, CG_ERR_ARG, "seg_off[0] must be 0");
+    for (uint32_t s = 0; s < b->n_segs; ++s) {
+        if (b->seg_off[s + 1] < b->seg_off[s]) return fail(h, CG_ERR_ARG, "seg_off is not non-decreasing at segment %u", s);
+        if (b->seg_len && b->seg_len[s] > b->seg_off[s + 1] - b->seg_off[s]) return fail(h, CG_ERR_ARG, "seg_len[%u] runs past seg_off[%u]", s, s + 1);
+    }
+    if (b->read_seg)
+        for (uint32_t r = 0; r < b->n_reads; ++r)
+            if (b->read_seg[r + 1] < b->read_seg[r]) return fail(h, CG_ERR_ARG, "read_seg is not non-decreasing at read %u", r);
+    for (uint64_t e = 0; e < b->n_exc; ++e)
+        if (b->exc_pos[e] >= b->seg_off[b->n_segs] || (e && b->exc_pos[e] <= b->exc_pos[e - 1])) return fail(h, CG_ERR_ARG, "exc_pos must be ascending batch positions (entry %llu)", (unsigned long long)e);
     return 0;
+}
+
+// packed input of the generic any-(k, w) kernel: expanded back to characters on the device
+__global__ void unpack_bases_kernel(const uint8_t *src, int format, uint64_t n, uint8_t *dst) {
+    const uint64_t stride = uint64_t(gridDim.x) * blockDim.x;
+    for (uint64_t i = blockIdx.x * uint64_t(blockDim.x) + threadIdx.x; i < n; i += stride) {
+        if (format == CG_BASES_RANK4) dst[i] = uint8_t("ACGNTNNN"[(src[i >> 1] >> ((i & 1u) * 4u)) & 7u]);
+        else dst[i] = uint8_t("ACGT"[(src[i >> 2] >> ((i & 3u) * 2u)) & 3u]);
+    }
+}
+__global__ void mark_exceptions_kernel(const unsigned long long *exc, uint64_t n_exc, uint8_t *dst) {
+    const uint64_t stride = uint64_t(gridDim.x) * blockDim.x;
+    for (uint64_t e = blockIdx.x * uint64_t(blockDim.x) + threadIdx.x; e < n_exc; e += stride) dst[exc[e]] = 'N';
 }
 
 // H2D of one batch (src/dehost_main.cpp:335-339: the chunk of records handed to the loop)
@@ -354,17 +396,29 @@ int stage(cg_handle *h, const cg_batch *b, const cg_read_scalars *sc) {
     int rc = validate_batch(h, b);
     if (rc) return rc;
     const uint64_t nbases = b->n_segs ? b->seg_off[b->n_segs] : 0;
-    // Packed transport: only the (19, 41) kernels decode it; in automatic mode tiny batches are not worth waking the pool for.
-    const bool pack = use_fast(h) && nbases > 0 && (h->host_pack_mode == 1 || (h->host_pack_mode < 0 && nbases >= PACK_MIN_BASES && cgh::threads() >= 8));
-    RSV(h, h->bases, (pack ? (nbases + 1) / 2 : nbases) + 64);
+    const int in_fmt = b->bases_format;
+    // Packed transport made by the library: only for ASCII input of the (19, 41) kernels; in automatic mode tiny batches are
+    // not worth waking the pool for.  Two-bit input is copied as it is; rank nibbles (and any packed input of the generic
+    // any-(k, w) kernel) are expanded back to characters on the device.
+    const bool pack = in_fmt == CG_BASES_ASCII && use_fast(h) && nbases > 0 &&
+                      (h->host_pack_mode == 1 || (h->host_pack_mode < 0 && nbases >= PACK_MIN_BASES && cgh::threads() >= 8));
+    const bool unpack = in_fmt == CG_BASES_RANK4 || (in_fmt == CG_BASES_2BIT && !use_fast(h));
+    const int dev_fmt = pack ? int(CG_BASES_2BIT) : (unpack ? int(CG_BASES_ASCII) : in_fmt);
+    const size_t in_bytes = in_fmt == CG_BASES_2BIT ? size_t((nbases + 3) / 4) : (in_fmt == CG_BASES_RANK4 ? size_t((nbases + 1) / 2) : size_t(nbases));
+    const size_t dev_bytes = dev_fmt == CG_BASES_2BIT ? size_t((nbases + 3) / 4) : size_t(nbases);
+    RSV(h, h->bases, dev_bytes + 64);
     RSV(h, h->seg_off, (size_t(b->n_segs) + 1) * 8);
     if (b->read_seg) RSV(h, h->read_seg, (size_t(b->n_reads) + 1) * 4);
+    if (b->seg_len) RSV(h, h->seg_len, size_t(b->n_segs) * 8 + 8);
     rc = reserve_outputs(h, b->n_reads);
     if (rc) return rc;
-    h->staged_packed = pack;
-    h->info.last_packed = pack ? 1 : 0; h->info.last_pack_ms = 0;
+    h->staged_packed = pack; h->staged_format = dev_fmt; h->staged_has_seg_len = b->seg_len != nullptr; h->staged_n_exc = 0;
+    h->info.last_packed = dev_fmt != CG_BASES_ASCII ? 1 : 0; h->info.last_pack_ms = 0;
+    const uint64_t *exc = b->exc_pos;      // exception list that goes with two-bit bases on the device
+    uint64_t n_exc = dev_fmt == CG_BASES_2BIT ? b->n_exc : 0;
+    std::vector<uint64_t> own_exc;
     if (pack) {
-        const size_t pbytes = size_t((nbases + 1) / 2);
+        const size_t pbytes = size_t((nbases + 3) / 4);
         auto &ps = h->pack;
         if (!ps.done) CU(h, cudaEventCreateWithFlags(&ps.done, cudaEventDisableTiming));
         if (ps.armed) { CU(h, cudaEventSynchronize(ps.done)); ps.armed = false; }   // previous copy out of the staging buffer is over
@@ -378,26 +432,59 @@ int stage(cg_handle *h, const cg_batch *b, const cg_read_scalars *sc) {
         CU(h, cudaEventRecord(h->ev[0], h->stream));
         cudaError_t ce = cudaSuccess;
         const auto t0 = std::chrono::steady_clock::now();
-        cgh::pack_chunked(reinterpret_cast<const uint8_t *>(b->bases), static_cast<uint8_t *>(ps.p), nbases, PACK_CHUNK_BASES,
-                          [&](uint64_t lo, uint64_t hi) {   // chunk [lo, hi) is packed (lo is even): its copy overlaps the packing of the next
-                              if (ce == cudaSuccess)
-                                  ce = cudaMemcpyAsync(h->bases.as<uint8_t>() + lo / 2, static_cast<const uint8_t *>(ps.p) + lo / 2, size_t((hi - lo + 1) / 2),
-                                                       cudaMemcpyHostToDevice, h->stream);
-                          });
+        cgh::pack2_chunked(reinterpret_cast<const uint8_t *>(b->bases), static_cast<uint8_t *>(ps.p), nbases, PACK_CHUNK_BASES,
+                           [&](uint64_t lo, uint64_t hi) {   // chunk [lo, hi) is packed (lo is a multiple of 4): its copy overlaps the packing of the next
+                               if (ce == cudaSuccess)
+                                   ce = cudaMemcpyAsync(h->bases.as<uint8_t>() + lo / 4, static_cast<const uint8_t *>(ps.p) + lo / 4, size_t((hi - lo + 3) / 4),
+                                                        cudaMemcpyHostToDevice, h->stream);
+                           }, own_exc);
         h->info.last_pack_ms = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - t0).count();
         CU(h, ce);
         CU(h, cudaEventRecord(ps.done, h->stream));
         ps.armed = true;
         h->info.last_h2d_bytes = pbytes;
+        exc = own_exc.data(); n_exc = own_exc.size();
+    } else if (unpack) {
+        CU(h, cudaEventRecord(h->ev[0], h->stream));
+        RSV(h, h->unpack_src, in_bytes + 64);
+        if (in_bytes) CU(h, cudaMemcpyAsync(h->unpack_src.p, b->bases, in_bytes, cudaMemcpyHostToDevice, h->stream));
+        if (b->n_exc) {
+            RSV(h, h->exc_pos, size_t(b->n_exc) * 8);
+            CU(h, cudaMemcpyAsync(h->exc_pos.p, b->exc_pos, size_t(b->n_exc) * 8, cudaMemcpyHostToDevice, h->stream));
+        }
+        if (nbases) {
+            unpack_bases_kernel<<<h->sm_count * 8, 256, 0, h->stream>>>(h->unpack_src.as<uint8_t>(), in_fmt, nbases, h->bases.as<uint8_t>());
+            if (b->n_exc) mark_exceptions_kernel<<<64, 256, 0, h->stream>>>(h->exc_pos.as<unsigned long long>(), b->n_exc, h->bases.as<uint8_t>());
+            CU(h, cudaGetLastError());
+        }
+        h->info.last_h2d_bytes = in_bytes + size_t(b->n_exc) * 8;
     } else {
         CU(h, cudaEventRecord(h->ev[0], h->stream));
-        if (nbases) CU(h, cudaMemcpyAsync(h->bases.p, b->bases, nbases, cudaMemcpyHostToDevice, h->stream));
-        h->info.last_h2d_bytes = nbases;
+        if (in_bytes) CU(h, cudaMemcpyAsync(h->bases.p, b->bases, in_bytes, cudaMemcpyHostToDevice, h->stream));
+        h->info.last_h2d_bytes = in_bytes;
     }
-    h->info.last_h2d_bytes += (size_t(b->n_segs) + 1) * 8 + (b->read_seg ? (size_t(b->n_reads) + 1) * 4 : 0) + (sc && b->n_reads ? size_t(b->n_reads) * 12 : 0);
+    if (dev_fmt == CG_BASES_2BIT && n_exc) {
+        // exception list + the index range of every segment in it (one merge pass; reads rarely hold an N)
+        if (n_exc > 0xFFFFFFF0ull) return fail(h, CG_ERR_ARG, "more than 2^32 non-ACGT bases in one batch");
+        std::vector<uint32_t> off(size_t(b->n_segs) + 1);
+        uint64_t e = 0;
+        for (uint32_t s = 0; s < b->n_segs; ++s) {
+            while (e < n_exc && exc[e] < b->seg_off[s]) ++e;
+            off[s] = uint32_t(e);
+        }
+        off[b->n_segs] = uint32_t(n_exc);
+        RSV(h, h->exc_pos, size_t(n_exc) * 8); RSV(h, h->exc_seg_off, off.size() * 4);
+        CU(h, cudaMemcpyAsync(h->exc_pos.p, exc, size_t(n_exc) * 8, cudaMemcpyHostToDevice, h->stream));
+        CU(h, cudaMemcpyAsync(h->exc_seg_off.p, off.data(), off.size() * 4, cudaMemcpyHostToDevice, h->stream));
+        CU(h, cudaStreamSynchronize(h->stream));   // `off` (and the library's own list) are pageable and die with this scope
+        h->staged_n_exc = n_exc;
+        h->info.last_h2d_bytes += size_t(n_exc) * 8 + off.size() * 4;
+    }
+    h->info.last_h2d_bytes += (size_t(b->n_segs) + 1) * 8 + (b->read_seg ? (size_t(b->n_reads) + 1) * 4 : 0) + (b->seg_len ? size_t(b->n_segs) * 8 : 0) + (sc && b->n_reads ? size_t(b->n_reads) * 12 : 0);
     static const uint64_t zero_off[1] = {0};
     CU(h, cudaMemcpyAsync(h->seg_off.p, b->n_segs ? b->seg_off : zero_off, (size_t(b->n_segs) + 1) * 8, cudaMemcpyHostToDevice, h->stream));
     if (b->read_seg) CU(h, cudaMemcpyAsync(h->read_seg.p, b->read_seg, (size_t(b->n_reads) + 1) * 4, cudaMemcpyHostToDevice, h->stream));
+    if (b->seg_len && b->n_segs) CU(h, cudaMemcpyAsync(h->seg_len.p, b->seg_len, size_t(b->n_segs) * 8, cudaMemcpyHostToDevice, h->stream));
     h->staged_has_scalars = false;
     if (sc && b->n_reads) {
         if (!sc->mean_quality || !sc->compression || !sc->length) return fail(h, CG_ERR_ARG, "null read scalars");
@@ -409,7 +496,7 @@ int stage(cg_handle *h, const cg_batch *b, const cg_read_scalars *sc) {
     CU(h, cudaEventRecord(h->ev[1], h->stream));
     h->staged_reads = b->n_reads; h->staged_segs = b->n_segs; h->staged_bases = nbases; h->staged_has_read_seg = b->read_seg != nullptr;
     h->staged_max_read_len = 0;
-    for (uint32_t r = 0; r < b->n_reads; ++r) {
+    for (uint32_t r = 0; r < b->n_reads; ++r) {   // span of the read in the buffer (>= its bases): only steers the long-read dispatch
         const uint32_t s0 = b->read_seg ? b->read_seg[r] : r, s1 = b->read_seg ? b->read_seg[r + 1] : r + 1;
         if (s1 > s0) h->staged_max_read_len = std::max<uint64_t>(h->staged_max_read_len, b->seg_off[s1] - b->seg_off[s0]);
     }

@@ -53,7 +53,13 @@ struct CountParams {
     uint32_t n_parts, my_part;
     uint32_t rows_per_part;             // rows are < 2^32 (bin_size <= 2^32 - 3)
     uint32_t async_gather;              // host-side choice of the warp kernel's AG instantiation (filter larger than L2); not read on the device
-    uint32_t packed;                    // bases are 4-bit dna5 ranks, two per byte (host_pack.hpp); only the (19, 41) kernels
+    uint32_t packed;                    // transport of `bases` (enum cg_bases_format): 0 ASCII or 2 two bits per base; 2 only in the
+                                        // (19, 41) kernels.  Rank nibbles (1), and packed input of the generic kernel, are unpacked by the library.
+    // CG_BASES_2BIT: ascending batch positions of the bases that are not A/C/G/T (they hash as N), and for every segment
+    // the index range [exc_seg_off[s], exc_seg_off[s + 1]) of its entries.  n_exc == 0: no such base in the batch.
+    const unsigned long long *exc_pos;
+    const uint32_t *exc_seg_off;
+    unsigned long long n_exc;
     const void *part_base[CG_MAX_PARTS];
 };
 

@@ -124,20 +124,64 @@ __device__ __forceinline__ bool neq64h(uint64_t a, uint64_t b) {
 // deliberately no "memory" clobber (the window-minimum loads around it must stay free to move): the caller fences once.
 __device__ __forceinline__ void st_shared_u64(uint32_t addr, uint64_t v) { asm volatile("st.shared.u64 [%0], %1;" ::"r"(addr), "l"(v)); }
 
-// Packed transport (host_pack.hpp): a nibble is the dna5 rank.  PRMT with the nibbles themselves as byte selectors expands
-// four bases per instruction into exactly the code bytes base_code() yields for ASCII (rank | complement rank << 4).
-constexpr uint32_t PK_TLO = 0x33122140u, PK_THI = 0x33333304u;   // code bytes of ranks 0..3 / 4..7 (5..7 never occur: N)
-__device__ __forceinline__ void decode_packed16(const uint4 x, uint4 &a, uint4 &b) {   // 32 bases -> 32 code bytes
-    a.x = __byte_perm(PK_TLO, PK_THI, x.x); a.y = __byte_perm(PK_TLO, PK_THI, x.x >> 16);
-    a.z = __byte_perm(PK_TLO, PK_THI, x.y); a.w = __byte_perm(PK_TLO, PK_THI, x.y >> 16);
-    b.x = __byte_perm(PK_TLO, PK_THI, x.z); b.y = __byte_perm(PK_TLO, PK_THI, x.z >> 16);
-    b.z = __byte_perm(PK_TLO, PK_THI, x.w); b.w = __byte_perm(PK_TLO, PK_THI, x.w >> 16);
+// Two-bit transport (CG_BASES_2BIT): A0 C1 G2 T3, sixteen bases per 32-bit word, base i at bits 2i.  The even and the odd
+// fields, masked apart, are nibble selectors into the four code bytes; two more PRMT per eight bases interleave them.
+constexpr uint32_t PK2_T = 0x04122140u;   // code bytes (rank | complement rank << 4) of A, C, G, T
+__device__ __forceinline__ uint4 decode_2bit16(uint32_t w) {   // 16 bases -> 16 code bytes
+    const uint32_t e = w & 0x33333333u, o = (w >> 2) & 0x33333333u;
+    const uint32_t el = __byte_perm(PK2_T, 0u, e), eh = __byte_perm(PK2_T, 0u, e >> 16);
+    const uint32_t ol = __byte_perm(PK2_T, 0u, o), oh = __byte_perm(PK2_T, 0u, o >> 16);
+    uint4 r;
+    r.x = __byte_perm(el, ol, 0x5140u); r.y = __byte_perm(el, ol, 0x7362u);
+    r.z = __byte_perm(eh, oh, 0x5140u); r.w = __byte_perm(eh, oh, 0x7362u);
+    return r;
 }
-// code byte of base i of the batch, either transport (cold paths only)
-__device__ __forceinline__ uint32_t code_at(const uint8_t *bases, bool packed, const uint8_t *lut, uint64_t i) {
-    if (!packed) return lut[bases[i]];
-    const uint32_t r = (uint32_t(bases[i >> 1]) >> ((uint32_t(i) & 1u) * 4u)) & 7u;
-    return uint32_t((((unsigned long long)PK_THI << 32) | PK_TLO) >> (8u * r)) & 0xFFu;
+// first index in [lo, hi) whose exception position is >= pos
+__device__ __forceinline__ uint32_t exc_lower_bound(const unsigned long long *exc, uint32_t lo, uint32_t hi, unsigned long long pos) {
+    while (lo < hi) { const uint32_t mid = (lo + hi) >> 1; if (exc[mid] < pos) lo = mid + 1; else hi = mid; }
+    return lo;
+}
+// The non-ACGT bases of batch positions [G, G + nb) of a two-bit tile become N in the code bytes (codes[0] = base G).
+// [lo, hi) = the segment's exception entries; threads t0, t0 + stride, ... share the work.  Cold: reads rarely hold an N.
+__device__ __noinline__ void patch_exceptions(const unsigned long long *exc, uint32_t lo, uint32_t hi, unsigned long long G, uint32_t nb,
+                                              uint8_t *codes, uint32_t t0, uint32_t stride) {
+    for (uint32_t e = exc_lower_bound(exc, lo, hi, G) + t0; e < hi; e += stride) {
+        const unsigned long long p = exc[e];
+        if (p >= G + nb) break;
+        codes[p - G] = 0x33;
+    }
+}
+// warp flavour: looks the segment's range up itself, so that the hot loop only spends one test on P.n_exc
+__device__ __noinline__ void patch_tile_warp(const CountParams &P, uint32_t seg, unsigned long long G, uint32_t nb, uint8_t *codes, uint32_t lane) {
+    const uint32_t lo = P.exc_seg_off[seg], hi = P.exc_seg_off[seg + 1];
+    if (hi > lo) {
+        __syncwarp();   // every lane's decoded vectors are in place before single bytes of them are overwritten
+        patch_exceptions(P.exc_pos, lo, hi, G, nb, codes, lane, 32u);
+    }
+}
+// code byte of base i of the batch (cold paths only: segments shorter than one window)
+__device__ __noinline__ uint32_t code_at_2bit(const CountParams &P, uint64_t i) {
+    if (P.n_exc) {
+        const uint32_t e = exc_lower_bound(P.exc_pos, 0u, uint32_t(P.n_exc), i);
+        if (e < P.n_exc && P.exc_pos[e] == i) return 0x33u;
+    }
+    const uint32_t r = (uint32_t(P.bases[i >> 2]) >> ((uint32_t(i) & 3u) * 2u)) & 3u;
+    return (PK2_T >> (8u * r)) & 0xFFu;
+}
+template <int FMT>
+__device__ __forceinline__ uint32_t code_at(const CountParams &P, const uint8_t *lut, uint64_t i) {
+    return FMT == 2 ? code_at_2bit(P, i) : uint32_t(lut[P.bases[i]]);
+}
+// seeded canonical value of the k-mer that starts at base i (cold paths only)
+template <int FMT, int KK>
+__device__ __noinline__ uint64_t kmer_value_slow(const CountParams &P, const uint8_t *lut, uint64_t i) {
+    uint64_t f = 0, rc = 0;
+#pragma unroll 1
+    for (int j = 0; j < KK; ++j) f = f * 5u + (code_at<FMT>(P, lut, i + j) & 15u);
+#pragma unroll 1
+    for (int j = KK; j-- > 0;) rc = rc * 5u + (code_at<FMT>(P, lut, i + j) >> 4);
+    f ^= P.seed; rc ^= P.seed;
+    return f < rc ? f : rc;
 }
 
 // per-read counters shared by the list phase and the inline (exact path) emission
@@ -352,12 +396,8 @@ __global__ void __launch_bounds__(NT2, CG_V2_MINB) count_kernel_v2(const __grid_
                     // ---- fewer k-mers than one window: a single window, a single emission (its minimum) ----
                     if (tid < 32) {
                         uint64_t best = VMAX;
-                        for (uint32_t i = lane; i < nkm; i += 32) {
-                            uint64_t f = 0, rc = 0;
-                            for (int j = 0; j < KK; ++j) f = f * 5u + (code_at(P.bases, P.packed != 0, S.lut, sbase + i + j) & 15u);
-                            for (int j = KK; j-- > 0;) rc = rc * 5u + (code_at(P.bases, P.packed != 0, S.lut, sbase + i + j) >> 4);
-                            best = umin64(best, umin64(f ^ seed, rc ^ seed));
-                        }
+                        for (uint32_t i = lane; i < nkm; i += 32)
+                            best = umin64(best, P.packed == 2 ? kmer_value_slow<2, KK>(P, S.lut, sbase + i) : kmer_value_slow<0, KK>(P, S.lut, sbase + i));
 #pragma unroll
                         for (int o = 16; o > 0; o >>= 1) best = umin64(best, __shfl_xor_sync(0xFFFFFFFFu, best, o));
                         if (lane == 0) { const Smem2 Sx = S; process_exact<MODE>(P, Sx, &s_nhash, best, do_tot, do_unq); }
@@ -375,15 +415,22 @@ __global__ void __launch_bounds__(NT2, CG_V2_MINB) count_kernel_v2(const __grid_
                     //      flight before the first use; codes[32 + head + i] = code of tile base i -----------------
                     const uint64_t G = sbase + g0;   // index of the tile's first base in the batch
                     const uint8_t *gsrc = P.bases + G;
-                    const uint32_t head = P.packed ? uint32_t(G & 31u) : uint32_t(reinterpret_cast<uintptr_t>(gsrc) & 15u);
-                    if (P.packed) {   // 16-byte vectors of 32 rank nibbles; one vector per thread covers a tile
-                        const uint4 *vsrc = reinterpret_cast<const uint4 *>(P.bases) + (G >> 5);
-                        const uint32_t nvec = (head + nb + 31u) >> 5;
-                        if (tid < nvec) {
-                            uint4 a, b;
-                            decode_packed16(ldg_stream_v4(vsrc + tid, pol_stream), a, b);
-                            *reinterpret_cast<uint4 *>(S.codes + 32 + 32 * tid) = a;
-                            *reinterpret_cast<uint4 *>(S.codes + 32 + 32 * tid + 16) = b;
+                    const uint32_t head = P.packed == 2 ? uint32_t(G & 63u) : uint32_t(reinterpret_cast<uintptr_t>(gsrc) & 15u);
+                    if (P.packed == 2) {   // 16-byte vectors of 64 two-bit bases: half a vector (32 bases) per thread
+                        const uint2 *vsrc = reinterpret_cast<const uint2 *>(P.bases) + ((G >> 6) << 1);
+                        const uint32_t nhalf = (head + nb + 31u) >> 5;
+                        if (tid < nhalf) {
+                            uint2 x;
+                            asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v2.u32 {%0, %1}, [%2], %3;" : "=r"(x.x), "=r"(x.y) : "l"(vsrc + tid), "l"(pol_stream));
+                            *reinterpret_cast<uint4 *>(S.codes + 32 + 32 * tid) = decode_2bit16(x.x);
+                            *reinterpret_cast<uint4 *>(S.codes + 32 + 32 * tid + 16) = decode_2bit16(x.y);
+                        }
+                        if (P.n_exc) {
+                            const uint32_t elo = P.exc_seg_off[seg], ehi = P.exc_seg_off[seg + 1];
+                            if (ehi > elo) {
+                                __syncthreads();
+                                patch_exceptions(P.exc_pos, elo, ehi, G, nb, S.codes + 32 + head, tid, NT2);
+                            }
                         }
                     } else {
                         const uint4 *vsrc = reinterpret_cast<const uint4 *>(gsrc - head);

@@ -37,9 +37,10 @@ namespace cgk {
 #ifndef CG_V3_MINB_AG
 #define CG_V3_MINB_AG 1
 #endif
-// warps per CTA (independent of each other) and resident CTAs per SM, per gather carrier
-template <bool AG> struct V3Shape {
-    static constexpr int WARPS = AG ? CG_V3_WARPS_AG : CG_V3_WARPS;
+// warps per CTA (independent of each other) and resident CTAs per SM, per gather carrier.  With more than 4 bins every warp
+// carries 4 KB of counters: 10 warps are what fits next to the landing slots of the gathers.
+template <bool AG, bool SMALL = true> struct V3Shape {
+    static constexpr int WARPS = AG ? (SMALL ? CG_V3_WARPS_AG : (CG_V3_WARPS_AG < 10 ? CG_V3_WARPS_AG : 10)) : CG_V3_WARPS;
     static constexpr int MINB = AG ? CG_V3_MINB_AG : CG_V3_MINB;
 };
 #ifndef CG_V3_WLIST_CAP
@@ -57,29 +58,33 @@ template <int KK, int WW, bool SMALL, bool AG = false> struct V3Cfg {
     static constexpr int CODES = ((32 + 16 * NVL * 32 + 64) + 15) / 16 * 16;
     static constexpr int GQ = AG ? CG_V3_DQA * 3 * 32 * 16 : 0;   // landing slots of the asynchronous gathers: 16 bytes per (group, hash function, lane)
     static constexpr int RAW = NVL * 32 * 16;     // cp.async staging of the next tile's bases (ASCII, or 32 rank nibbles per vector)
-    static_assert((31 + NB + 31) / 32 <= 32, "packed transport: one vector per lane must cover a tile");
+    static_assert((63 + NB + 31) / 32 <= 32, "packed transports: 32 bases per lane must cover a tile");
     // a lane that overruns its PRIV_CAP slots (such a tile is redone exactly) spills into its right neighbour's slots; lane 31
     // spills into PRIV_GUARD, never into the list, whose head holds minimisers still waiting for a full gather group
     static constexpr int PRIV_GUARD = WW + 1 - PRIV_CAP > 0 ? WW + 1 - PRIV_CAP : 0;
     static constexpr size_t WARP_BYTES = size_t(NK) * 8 + (size_t(32) * PRIV_CAP + PRIV_GUARD) * 8 + size_t(WLIST_CAP) * 8 + size_t(NCNT) * 8 + 32 +
                                          size_t(NCNT) * 4 * 2 + CODES + RAW + GQ;
-    static constexpr size_t SMEM = 512 + V3Shape<AG>::WARPS * WARP_BYTES;
+    static constexpr size_t SMEM = 512 + V3Shape<AG, SMALL>::WARPS * WARP_BYTES;
+    static_assert(SMEM <= 227 * 1024, "a CTA of the warp-per-read kernel must fit the 227 KB of shared memory of an SM");
     static_assert(((size_t(32) * PRIV_CAP + PRIV_GUARD) * 8) % 16 == 0 && CODES % 16 == 0 && WARP_BYTES % 16 == 0,
                   "the staging vectors behind the slots need 16-byte alignment");
 };
 
-template <int MODE, int KK, int WW, bool SMALL, bool AG = false>
+// FMT: transport of the bases the kernel decodes (enum cg_bases_format: 0 ASCII, 2 two bits per base) — a template parameter:
+// with the format a run-time value the three-way address arithmetic costs the hot loop registers (+5 % kernel time measured).
+template <int MODE, int KK, int WW, bool SMALL, bool AG = false, int FMT = 0>
 #ifdef CG_V3_MAXNREG
 __global__ void __maxnreg__(CG_V3_MAXNREG)
 #else
-__global__ void __launch_bounds__(V3Shape<AG>::WARPS * 32, V3Shape<AG>::MINB)
+__global__ void __launch_bounds__(V3Shape<AG, SMALL>::WARPS * 32, V3Shape<AG, SMALL>::MINB)
 #endif
 count_kernel_v3(const __grid_constant__ CountParams P) {
     using C2 = V2Cfg<KK, WW>;
     using C = V3Cfg<KK, WW, SMALL, AG && MODE == 0>;
     constexpr int NW = ModeTraits<MODE>::NW;
     constexpr int KL = C2::KL, KH = C2::KH;
-    constexpr int WARPS3 = V3Shape<AG>::WARPS;
+    constexpr int WARPS3 = V3Shape<AG, SMALL>::WARPS;
+    static_assert(FMT == 0 || FMT == 2, "the kernels decode ASCII or two-bit bases; rank nibbles are unpacked by the library");
     static_assert(!AG || MODE == 0, "the cp.async carrier only exists for narrow rows");
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
@@ -125,18 +130,20 @@ count_kernel_v3(const __grid_constant__ CountParams P) {
     // ASCII transport: 16 bases per vector, aligned in global memory; packed transport: 32 rank nibbles per vector.
     // (P is also passed by reference to out-of-line helpers, so it has a local-memory copy: the lambdas below must capture plain
     // values, not P, or every use turns into a local load inside the hot loop)
-    const bool packed = P.packed != 0;
+    constexpr uint32_t fmt = FMT;    // 0 ASCII (16 bases per staged vector), 2 two bits per base (64 per vector)
     const uint8_t *const gbases = P.bases;
     uint64_t pf_tag = 0;
     const uint32_t gq_s = uint32_t(__cvta_generic_to_shared(S.codes + C::CODES + C::RAW)) + lane * 16u;
     const uint32_t raw_s = uint32_t(__cvta_generic_to_shared(raw));
     auto tile_head = [&](uint64_t G) -> uint32_t {
-        return packed ? uint32_t(G & 31u) : uint32_t(reinterpret_cast<uintptr_t>(gbases + G) & 15u);
+        return fmt == 2 ? uint32_t(G & 63u) : uint32_t(reinterpret_cast<uintptr_t>(gbases + G) & 15u);
     };
-    auto tile_nvec = [&](uint32_t head, uint32_t nb) -> uint32_t { return packed ? (head + nb + 31u) >> 5 : (head + nb + 15u) >> 4; };
+    auto tile_nvec = [&](uint32_t head, uint32_t nb) -> uint32_t {
+        return fmt == 2 ? (head + nb + 63u) >> 6 : (head + nb + 15u) >> 4;
+    };
     auto prefetch = [&](uint64_t G, uint32_t nb) {
         const uint32_t head = tile_head(G);
-        const uint4 *vsrc = packed ? reinterpret_cast<const uint4 *>(gbases) + (G >> 5) : reinterpret_cast<const uint4 *>(gbases + G - head);
+        const uint4 *vsrc = fmt == 2 ? reinterpret_cast<const uint4 *>(gbases) + (G >> 6) : reinterpret_cast<const uint4 *>(gbases + G - head);
         const uint32_t nvec = tile_nvec(head, nb);
 #pragma unroll
         for (int q = 0; q < C::NVL; ++q) {
@@ -307,12 +314,7 @@ count_kernel_v3(const __grid_constant__ CountParams P) {
                 const uint64_t nkm = slen - KK + 1;
                 if (nkm < WW) {   // a single window: its minimum is the only emission
                     uint64_t best = VMAX;
-                    for (uint32_t i = lane; i < nkm; i += 32) {
-                        uint64_t f = 0, rc = 0;
-                        for (int j = 0; j < KK; ++j) f = f * 5u + (code_at(gbases, packed, S.lut, sbase + i + j) & 15u);
-                        for (int j = KK; j-- > 0;) rc = rc * 5u + (code_at(gbases, packed, S.lut, sbase + i + j) >> 4);
-                        best = umin64(best, umin64(f ^ seed, rc ^ seed));
-                    }
+                    for (uint32_t i = lane; i < nkm; i += 32) best = umin64(best, kmer_value_slow<FMT, KK>(P, S.lut, sbase + i));
 #pragma unroll
                     for (int o = 16; o > 0; o >>= 1) best = umin64(best, __shfl_xor_sync(0xFFFFFFFFu, best, o));
                     if (lane == 0) { const Smem2 Sx = S; process_exact<MODE>(P, Sx, s_nhash, best, do_tot, do_unq); }   // a copy: S itself must never have its address taken
@@ -343,13 +345,13 @@ count_kernel_v3(const __grid_constant__ CountParams P) {
                         asm volatile("cp.async.wait_all;" ::: "memory");
                     }
                     __syncwarp();                                      // staging complete for every lane; previous tile's readers of codes are done
-                    if (packed) {
-                        if (lane < nvec) {   // a tile is at most 26 vectors of 32 bases
-                            uint4 a, b;
-                            decode_packed16(raw[lane], a, b);
-                            *reinterpret_cast<uint4 *>(S.codes + 32 + 32 * lane) = a;
-                            *reinterpret_cast<uint4 *>(S.codes + 32 + 32 * lane + 16) = b;
+                    if (fmt == 2) {
+                        if (lane < ((head + nb + 31u) >> 5)) {   // half a vector (32 bases) per lane
+                            const uint2 x = reinterpret_cast<const uint2 *>(raw)[lane];
+                            *reinterpret_cast<uint4 *>(S.codes + 32 + 32 * lane) = decode_2bit16(x.x);
+                            *reinterpret_cast<uint4 *>(S.codes + 32 + 32 * lane + 16) = decode_2bit16(x.y);
                         }
+                        if (P.n_exc) patch_tile_warp(P, seg, G, nb, S.codes + 32 + head, lane);   // the batch holds bases that are not A/C/G/T
                     } else {
 #pragma unroll
                         for (int q = 0; q < C::NVL; ++q) {

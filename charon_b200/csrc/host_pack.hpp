@@ -11,6 +11,7 @@
 #include <cstddef>
 #include <cstdint>
 #include <functional>
+#include <vector>
 
 namespace cgh {
 
@@ -24,11 +25,19 @@ inline uint8_t rank_of(uint8_t c) {
 // except the last one when end is odd (its high nibble becomes 0).  Single-threaded.
 void pack_range(const uint8_t *src, uint8_t *dst, uint64_t begin, uint64_t end);
 
+// CG_BASES_2BIT writer for one run of bases (include/charon_gpu.h cg_pack_bases_2bit): dst gets (n + 3) / 4 bytes, base i =
+// bits 2 * (i & 3) of dst[i >> 2], A0 C1 G2 T3 (U -> T); every other character is stored as 0 and its position pos0 + i is
+// appended to exc (at most cap entries are stored).  Returns how many such characters the run holds.  Single-threaded.
+uint64_t pack2_range(const uint8_t *src, uint64_t n, uint8_t *dst, uint64_t pos0, uint64_t *exc, uint64_t cap);
+
 // Thread pool shared by all handles of the process.  threads() resolves CHARON_HOST_THREADS, else min(16, hardware).
 int threads();
 void set_threads(int n);   // takes effect before the first job, or re-creates the pool
 // Packs [0, n) in blocks on the pool (the caller packs too); after every `chunk` bases (a multiple of 64) that are complete,
 // and in order, on_chunk(begin_base, end_base) is called on the CALLER's thread (it enqueues that chunk's H2D copy).
 void pack_chunked(const uint8_t *src, uint8_t *dst, uint64_t n, uint64_t chunk, const std::function<void(uint64_t, uint64_t)> &on_chunk);
+// The same to two bits per base (pack2_range per block); exc receives the ascending positions of everything that is not A/C/G/T/U.
+void pack2_chunked(const uint8_t *src, uint8_t *dst, uint64_t n, uint64_t chunk, const std::function<void(uint64_t, uint64_t)> &on_chunk,
+                   std::vector<uint64_t> &exc);
 
 }  // namespace cgh

@@ -6,37 +6,94 @@
 #include <omp.h>
 
 #include <algorithm>
+#include <chrono>
+#include <condition_variable>
+#include <deque>
+#include <exception>
 #include <iostream>
+#include <mutex>
 
 #include "cli.hpp"
 #include "runner.hpp"
 
 namespace charon_host {
 
-struct PinnedBuf {   // pinned host staging for the concatenated bases of one GPU's share of a batch
-    char *p = nullptr;
+// pinned host array (cudaHostAlloc through the library): what the copy engines read and write
+template <class T> struct Pinned {
+    T *p = nullptr;
     size_t cap = 0;
     void reserve(size_t n) {
         if (n <= cap) return;
         if (p) cg_host_free(p);
+        p = nullptr; cap = 0;
         void *q = nullptr;
-        const size_t want = n + n / 4 + 4096;
-        if (cg_host_alloc(want, &q) != 0) throw std::runtime_error(std::string("pinned allocation failed: ") + cg_last_error(nullptr));
-        p = static_cast<char *>(q); cap = want;
+        const size_t want = n + n / 4 + 64;
+        if (cg_host_alloc(want * sizeof(T), &q) != 0) throw std::runtime_error(std::string("pinned allocation failed: ") + cg_last_error(nullptr));
+        p = static_cast<T *>(q); cap = want;
     }
-    ~PinnedBuf() { if (p) cg_host_free(p); }
+    T &operator[](size_t i) { return p[i]; }
+    Pinned() = default;
+    Pinned(const Pinned &) = delete;
+    Pinned &operator=(const Pinned &) = delete;
+    ~Pinned() { if (p) cg_host_free(p); }
 };
 
-struct GpuSlice {   // what one GPU gets of a batch
+// One GPU's share of one batch, in the form the library takes it: CG_BASES_2BIT bases written while the per-read scalars
+// are computed (every segment on a 64-base boundary), offsets, scalars, and the outputs the GPU copies back.  Two of
+// these per GPU = the two pipeline slots of cg_submit_batch / cg_wait_batch.
+struct SlotBuf {
+    Pinned<uint8_t> packed;
+    Pinned<uint64_t> seg_off, seg_len, exc;
+    Pinned<uint32_t> read_seg, length, num_hashes, counts, unique_counts;
+    Pinned<float> mq, cr;
+    Pinned<double> prob;
+    Pinned<uint8_t> call, conf;
+    size_t r0 = 0, n_reads = 0, n_segs = 0, n_exc = 0;
+    uint64_t total_bases = 0;
+};
+
+struct GpuSlice {   // one GPU: its handle and its two slots
     cg_handle *h = nullptr;
-    PinnedBuf bases;
-    std::vector<uint64_t> seg_off;
-    std::vector<uint32_t> read_seg, length, num_hashes, counts, unique_counts;
-    std::vector<float> mq, cr;
-    std::vector<double> prob;
-    std::vector<uint8_t> call, conf;
-    int rc = 0;
-    std::string err;
+    SlotBuf slot[2];
+};
+
+// A batch of reads on its way through the pipeline: parsed by the reader thread, scalars + packing by the -t team,
+// classified on the GPU(s) (slot = batch number & 1), printed by the writer thread.
+struct Batch {
+    std::vector<ReadRow> rows;
+    std::vector<std::vector<uint64_t>> read_exc;   // per read: batch positions of its non-ACGT bases (almost always empty)
+    uint64_t seq = 0;
+    bool paired_mismatch = false;                  // reader: the pair after the last row of this batch has differing ids
+    std::string mismatch_text;
+};
+
+template <class T> class BoundedQueue {
+public:
+    explicit BoundedQueue(size_t cap) : cap_(cap) {}
+    bool push(T &&v) {
+        std::unique_lock<std::mutex> g(m_);
+        not_full_.wait(g, [&] { return q_.size() < cap_ || closed_; });
+        if (closed_) return false;
+        q_.push_back(std::move(v));
+        not_empty_.notify_one();
+        return true;
+    }
+    bool pop(T &out) {
+        std::unique_lock<std::mutex> g(m_);
+        not_empty_.wait(g, [&] { return !q_.empty() || closed_; });
+        if (q_.empty()) return false;
+        out = std::move(q_.front());
+        q_.pop_front();
+        not_full_.notify_one();
+        return true;
+    }
+    void close() { std::lock_guard<std::mutex> g(m_); closed_ = true; not_empty_.notify_all(); not_full_.notify_all(); }
+private:
+    std::mutex m_;
+    std::condition_variable not_empty_, not_full_;
+    std::deque<T> q_;
+    size_t cap_;
+    bool closed_ = false;
 };
 
 class Runner {
@@ -76,7 +133,7 @@ public:
                 std::fprintf(stderr, "charon: GPU %d: %s\n", g, m.c_str());
                 return 1;
             }
-            cg_set_host_pack(s->h, -1, std::max(1, int(opt_.threads)));   // -t also sizes the library's packing pool
+            cg_set_host_pack(s->h, 0, 0);   // the reads reach the library already packed (prepare_batch)
             gpu_.push_back(std::move(s));
         }
         if (opt_.partition_filter && opt_.gpus > 1)
@@ -94,9 +151,7 @@ public:
         classified_counts_.assign(ncat_, 0);
         if (opt_.is_paired) CH_INFO(log_, "%s files %s and %s", opt_.dehost ? "Dehosting" : "Classifying", opt_.read_file.c_str(), opt_.read_file2.c_str());
         else CH_INFO(log_, "%s file %s", opt_.dehost ? "Dehosting" : "Classifying", opt_.read_file.c_str());
-        read_loop();
-        complete();
-        flush_out();
+        run_pipeline();
         CH_INFO(log_, "Results summary: ");
         for (size_t i = 0; i < ncat_; ++i) CH_INFO(log_, "%s :\t\t%llu", idx_.categories[i].c_str(), (unsigned long long)classified_counts_[i]);
         CH_INFO(log_, "unclassified :\t%llu", (unsigned long long)unclassified_);
@@ -133,13 +188,16 @@ private:
             for (auto &p : kv.second) extract_[kv.first].emplace_back(new ExtractWriter(p, fastq));
     }
 
-    void read_loop();
-    void process_batch(std::vector<ReadRow> &rows);
-    void gpu_pass(std::vector<ReadRow> &rows, bool with_eval);
+    void run_pipeline();
+    void reader_thread(BoundedQueue<Batch> &parsed);
+    void writer_thread(BoundedQueue<std::vector<ReadRow>> &done);
+    void prepare_batch(Batch &b, int slot);
+    void submit_batch(Batch &b, int slot, bool with_eval);
+    void collect_batch(Batch &b, int slot, bool with_eval);
+    void train_batch(Batch &b, std::vector<ReadRow> &to_print);
     void eval_rows(std::vector<ReadRow *> &rows);
     void add_read(ReadRow &row, std::vector<ReadRow *> &pending, std::vector<ReadRow> &moved_cache);
     void emit(ReadRow &row);
-    void complete();
     void flush_out() { if (!out_.empty()) { std::fwrite(out_.data(), 1, out_.size(), stdout); out_.clear(); } std::fflush(stdout); }
     void upload_model() { for (auto &s : gpu_) if (model_.upload(s->h, host_index_) != 0) throw std::runtime_error(std::string("cg_set_model: ") + cg_last_error(s->h)); }
 
@@ -159,6 +217,8 @@ private:
     std::map<uint8_t, std::vector<std::unique_ptr<ExtractWriter>>> extract_;
     bool extract_open_ = false, input_fastq_ = true;
     std::string out_;
+    std::exception_ptr reader_err_, writer_err_;
+    double t_prepare_ = 0, t_gpu_wait_ = 0, t_reader_ = 0, t_writer_ = 0;   // stage wall times (charon.log, -v)
 };
 
 }  // namespace charon_host

@@ -90,16 +90,34 @@ typedef struct cg_thresholds {
 
 enum cg_mode { CG_MODE_DEHOST = 0 /* ReadEntry::call_host */, CG_MODE_CLASSIFY = 1 /* ReadEntry::call_category */ };
 
-/* A batch of reads.  bases = concatenated raw ASCII sequence characters (any case, IUPAC);
- * segment s is bases[seg_off[s] .. seg_off[s+1]); read r owns segments read_seg[r] .. read_seg[r+1]
- * (1 for single-end, 2 for paired: src/dehost_main.cpp:458-465).  read_seg may be NULL: one
- * segment per read. */
+/* How the bases of a batch are encoded.  The reference's parser hands the loop `std::vector<seqan3::dna5>` records
+ * (include/utils.hpp:17-19, src/dehost_main.cpp:335-339): one rank per base.  ASCII is accepted for convenience; the two
+ * packed formats are what a parser written for this library emits directly (host/fastx.hpp does), so that nothing has to
+ * be re-encoded between the file and the PCIe copy.  Offsets (seg_off, seg_len, exc_pos) always count BASES. */
+enum cg_bases_format {
+    CG_BASES_ASCII = 0,  /* one character per base, any case, IUPAC; U -> T, anything but ACGTU -> N */
+    CG_BASES_RANK4 = 1,  /* dna5 ranks (A0 C1 G2 N3 T4), 4 bits per base: base i = nibble (i & 1) of byte i >> 1 (cg_pack_bases) */
+    CG_BASES_2BIT = 2    /* A0 C1 G2 T3, 2 bits per base: base i = bits 2*(i & 3).. of byte i >> 2; every base that is not
+                            A/C/G/T/U is stored as 0 and listed in exc_pos (it hashes as N, like in the other formats)
+                            (cg_pack_bases_2bit).  The buffer must be readable up to the next multiple of 16 bytes. */
+};
+
+/* A batch of reads.  Segment s holds bases [seg_off[s], seg_off[s] + len(s)) of the batch, len(s) = seg_len[s] when
+ * seg_len is given, else seg_off[s + 1] - seg_off[s] (back-to-back segments).  With seg_len a producer may start every
+ * segment where it likes (e.g. on a 64-base boundary so that reads are packed independently of each other): the bases
+ * between the end of a segment and seg_off[s + 1] are padding and are never looked at.  Read r owns segments
+ * read_seg[r] .. read_seg[r+1] (1 for single-end, 2 for paired: src/dehost_main.cpp:458-465); read_seg may be NULL: one
+ * segment per read.  A zero-initialised tail (bases_format .. n_exc = 0) means back-to-back ASCII, as in round 1. */
 typedef struct cg_batch {
     const char *bases;
-    const uint64_t *seg_off;   /* n_segs + 1 entries */
+    const uint64_t *seg_off;   /* n_segs + 1 entries, non-decreasing, seg_off[0] = 0; seg_off[n_segs] = bases in the buffer */
     const uint32_t *read_seg;  /* n_reads + 1 entries or NULL */
     uint32_t n_reads;
     uint32_t n_segs;
+    int32_t bases_format;      /* enum cg_bases_format */
+    const uint64_t *seg_len;   /* n_segs entries or NULL */
+    const uint64_t *exc_pos;   /* CG_BASES_2BIT: ascending batch positions of the bases that are not A/C/G/T/U; NULL when n_exc = 0 */
+    uint64_t n_exc;
 } cg_batch;
 
 /* Per-read integer outputs of ReadEntry::get_counts (include/read_entry.hpp:92-138). */
@@ -218,6 +236,13 @@ int cg_fetch_staged(cg_handle *h, const cg_counts_out *counts_out, const cg_call
 int cg_set_host_pack(cg_handle *h, int mode, int threads);
 /* packed[i >> 1] nibble (i & 1) = dna5 rank of bases[i] (A0 C1 G2 N3 T4; U -> T, anything else -> N); (n + 1) / 2 bytes. Host only. */
 int cg_pack_bases(const char *bases, uint64_t n, uint8_t *packed);
+/* CG_BASES_2BIT writer for ONE run of bases (host only, single-threaded, SIMD; call it from as many threads as there are
+ * readers).  packed receives (n + 3) / 4 bytes: base i of the run = bits 2*(i & 3) of packed[i >> 2], so the run must start
+ * on a byte boundary of the batch buffer (pos0 % 4 == 0; pos0 = batch position of the run's first base).  Positions
+ * (pos0 + i) of the bases that are not A/C/G/T/U are appended to exc_pos (capacity exc_cap entries) in ascending order;
+ * *n_exc receives how many there were — when it exceeds exc_cap only the first exc_cap were stored.  This is the char ->
+ * dna5 conversion of the reference's parser (include/utils.hpp:17-19) fused with the packing. */
+int cg_pack_bases_2bit(const char *bases, uint64_t n, uint8_t *packed, uint64_t pos0, uint64_t *exc_pos, uint64_t exc_cap, uint64_t *n_exc);
 
 int cg_host_alloc(size_t bytes, void **out);   /* cudaHostAlloc: pinned buffers for cg_batch / outputs */
 void cg_host_free(void *p);

@@ -57,6 +57,7 @@ def lib():
     L.orc_classify_batch.argtypes = [vp, C.POINTER(Options), vp, vp, vp, u32, vp, vp, i32, i32, vp, vp, vp, vp, vp, vp, vp]
     L.orc_classify_batch.restype = f64
     L.orc_run_tsv.argtypes = [vp, C.POINTER(Options), C.c_char_p, vp, vp, vp, u32, vp, vp]; L.orc_run_tsv.restype = vp
+    L.orc_run_like_reference.argtypes = [vp, C.POINTER(Options), vp, u64, i32, u32, C.c_char_p, vp]; L.orc_run_like_reference.restype = C.c_longlong
     L.orc_free.argtypes = [vp]
     L.orc_max_threads.restype = i32
     _lib_cache = L
@@ -186,6 +187,19 @@ class Index:
         s = C.string_at(p).decode()
         lib().orc_free(p)
         return s
+
+    def run_like_reference(self, fastq: bytes, threads=1, chunk=100, tsv_path=None, opts=None):
+        """`charon dehost|classify -t threads` restated over an in-memory FASTQ (orc_run_like_reference): parse, chunks of
+        `chunk` reads, OpenMP over a chunk, one critical section for model + call + print.  Returns a dict of stage times."""
+        o = opts or default_options(True)
+        buf = np.frombuffer(fastq, np.uint8)
+        st = np.zeros(5, np.float64)
+        n = lib().orc_run_like_reference(self._h, C.byref(o), buf.ctypes.data, len(buf), threads, chunk,
+                                         tsv_path.encode() if tsv_path else None, st.ctypes.data)
+        if n < 0:
+            raise RuntimeError(f"orc_run_like_reference failed ({n})")
+        return dict(reads=int(n), threads=threads, parse_s=float(st[0]), loop_wall_s=float(st[1]), gzip_cpu_s=float(st[2]),
+                    hot_path_cpu_s=float(st[3]), model_print_cpu_s=float(st[4]))
 
     def __del__(self):
         try:

@@ -215,6 +215,85 @@ char *orc_run_tsv(orc_index *h, const orc_options *o, const char *ids, const cha
     std::memcpy(out, res.out.c_str(), res.out.size() + 1);
     return out;
 }
+// The reference program's own shape over an in-memory FASTQ text (src/dehost_main.cpp:314-381): records parsed serially,
+// chunks of `chunk` reads (default 100, include/dehost_arguments.hpp:22), `omp parallel for` over a chunk with the per-read
+// scalars (id token, length, mean quality :355-360, gzip ratio of the upper-case dna5 string :361-363), the hot path
+// (:366-373) and, inside ONE critical section (:374), model + call + TSV row.  The TSV goes to `tsv_path` (tmpfs file or
+// /dev/null; NULL = discarded).  stage_s[5] = wall seconds of {parse, whole loop}, then CPU seconds summed over threads of
+// {gzip ratio, minimiser + query + count, model + call + print}.  Returns the number of reads seen, <0 on error.
+long long orc_run_like_reference(orc_index *h, const orc_options *o, const char *fastq, uint64_t fastq_len, int threads, uint32_t chunk,
+                                 const char *tsv_path, double *stage_s) {
+    using clk = std::chrono::steady_clock;
+    auto secs = [](clk::time_point a, clk::time_point b) { return std::chrono::duration<double>(b - a).count(); };
+    Options opt = to_opt(o);
+    const Index &idx = h->idx;
+    Result res(opt, idx.summary);
+    res.keep_rows = false;
+    struct Rec { const char *id; size_t id_len; const char *seq; size_t seq_len; const char *qual; };
+    std::vector<Rec> recs;
+    const auto t0 = clk::now();
+    {   // FASTQ, four lines per record (what sequence_file_input sees in the synthetic files)
+        const char *p = fastq, *end = fastq + fastq_len;
+        auto line = [&](const char *&b, size_t &n) -> bool {
+            if (p >= end) return false;
+            const char *q = static_cast<const char *>(std::memchr(p, '\n', size_t(end - p)));
+            if (!q) q = end;
+            b = p; n = size_t(q - p); p = q < end ? q + 1 : end;
+            return true;
+        };
+        for (;;) {
+            Rec r{}; const char *plus; size_t nplus, nq;
+            if (!line(r.id, r.id_len)) break;
+            if (!r.id_len || r.id[0] != '@') return -1;
+            ++r.id; --r.id_len;
+            if (!line(r.seq, r.seq_len) || !line(plus, nplus) || !line(r.qual, nq) || nq != r.seq_len) return -1;
+            recs.push_back(r);
+        }
+    }
+    const auto t1 = clk::now();
+    FILE *out = tsv_path ? std::fopen(tsv_path, "w") : nullptr;
+    if (tsv_path && !out) return -2;
+    double cpu_gzip = 0, cpu_hot = 0, cpu_model = 0;
+    const uint8_t host_idx = idx.summary.host_category_index();
+    (void)host_idx;
+    if (!chunk) chunk = 100;
+    for (size_t c0 = 0; c0 < recs.size(); c0 += chunk) {
+        const size_t c1 = std::min(recs.size(), c0 + size_t(chunk));
+#pragma omp parallel for schedule(static) num_threads(threads > 0 ? threads : 1) reduction(+ : cpu_gzip, cpu_hot)
+        for (size_t i = c0; i < c1; ++i) {
+            const Rec &r = recs[i];
+            if (r.seq_len == 0) continue;                                  // :351-354
+            const auto a = clk::now();
+            std::string id(r.id, r.id_len);
+            uint64_t qsum = 0;
+            for (size_t j = 0; j < r.seq_len; ++j) qsum += uint64_t((unsigned char)r.qual[j] - 33);
+            const float mean_q = float(qsum / r.seq_len);                  // integer division, then float (:355-360)
+            std::string up(r.seq_len, 'N');
+            for (size_t j = 0; j < r.seq_len; ++j) up[j] = dna5_char(dna5_rank((unsigned char)r.seq[j]));
+            const float cr = compression_ratio(up.data(), up.size());
+            const auto b = clk::now();
+            ReadEntry e = process_read(idx, id, r.seq, r.seq_len, nullptr, 0, mean_q, cr);
+            const auto c = clk::now();
+            cpu_gzip += secs(a, b); cpu_hot += secs(b, c);
+#pragma omp critical(add_read_to_results)
+            {
+                const auto d = clk::now();
+                const size_t before = res.out.size();
+                res.add_read(e);
+                if (res.out.size() > before) {
+                    if (out) std::fwrite(res.out.data(), 1, res.out.size(), out);
+                    res.out.clear();
+                }
+                cpu_model += secs(d, clk::now());
+            }
+        }
+    }
+    res.complete();
+    if (out) { std::fwrite(res.out.data(), 1, res.out.size(), out); std::fclose(out); }
+    const auto t2 = clk::now();
+    if (stage_s) { stage_s[0] = secs(t0, t1); stage_s[1] = secs(t1, t2); stage_s[2] = cpu_gzip; stage_s[3] = cpu_hot; stage_s[4] = cpu_model; }
+    return (long long)recs.size();
+}
 void orc_free(void *p) { std::free(p); }
 int orc_max_threads() {
 #ifdef _OPENMP

@@ -103,7 +103,8 @@ def test_ragged_odd_offsets_long_reads_and_pairs(small, mode):
 
 @pytest.mark.gpu
 def test_pipeline_with_packing_and_transport_switches(small):
-    """Two slots in flight with packed batches, then the same batches as ASCII: identical integers; the copied byte count halves."""
+    """Two slots in flight with packed batches, then the same batches as ASCII: identical integers; the library's own packing
+    (two bits per base since round 2) quarters the copied bases."""
     idx, refs, gpu = small
     n, L = 3000, 4001            # odd read length: every other read starts on a high nibble
     batches = []
@@ -124,7 +125,7 @@ def test_pipeline_with_packing_and_transport_switches(small):
         gpu.select_slot(0)
         sent[mode] = gpu.info().last_h2d_bytes
     gpu.set_host_pack(-1)
-    assert sent[0] - sent[1] == n * L - (n * L + 1) // 2
+    assert sent[0] - sent[1] == n * L - (n * L + 3) // 4
 
 
 @pytest.mark.gpu
