@@ -273,13 +273,32 @@ def run_b200(args, name, wl):
     t0 = time.time()
     gpu = charon_b200.GpuClassifier.from_references(records, rec_bin, list(range(nb)), ncat, device=local_rank)   # index built on the GPU
     build_s = time.time() - t0
+    part_check = None
     if partitioned:
         # BASELINE config 4: the filter is split by row range over the ranks; rows owned by a peer are fetched through its
         # NVLink peer mapping inside the count kernel.  Reads stay sharded, still no data-path collective.
         import torch
         from charon_b200 import multi
+        # the same sample classified on the whole filter first (every rank still holds it here) and again once it is split
+        gpu.set_model(charon_b200.DehostOptions() if wl["mode"] == "dehost" else charon_b200.ClassifyOptions(), host_index=0)
+        n_chk = 20_000
+        cb_, co_, _ = make_reads(wl, records, rec_bin, n_chk, first_index=40_000_000 + rank * n_chk)
+        chk_args = (cb_, co_, np.full(n_chk, 20.0, np.float32), np.full(n_chk, 0.3, np.float32), np.full(n_chk, wl["read_len"], np.uint32))
+        whole = gpu.classify_batch(*chk_args)
+        replicated_bytes = int(gpu.info().filter_bytes)
         gpu.partition(rank, world)
         multi.exchange_partitions(gpu, dist, rank, world, device=torch.device("cuda", local_rank))
+        split = gpu.classify_batch(*chk_args)
+        same = all(np.array_equal(whole[k], split[k]) for k in ("num_hashes", "counts", "unique_counts", "call", "confidence")) and \
+            np.array_equal(whole["prob"], split["prob"], equal_nan=True)
+        t = torch.tensor([0 if same else 1], dtype=torch.int32, device="cuda")
+        dist.all_reduce(t)
+        part_check = {"partitioned_equals_replicated": int(t.item()) == 0, "reads_checked_per_rank": n_chk, "ranks": world,
+                      "filter_bytes_replicated": replicated_bytes, "filter_bytes_per_gpu_partitioned": int(gpu.info().filter_bytes)}
+        if int(t.item()) != 0:
+            if rank == 0:
+                sys.stderr.write("bench.py: PARITY FAILURE: the partitioned filter does not give the replicated filter's outputs\n")
+            os._exit(3)
     opts = charon_b200.DehostOptions() if wl["mode"] == "dehost" else charon_b200.ClassifyOptions()
     gpu.set_model(opts, host_index=0)
     pack_threads = max(1, min(16, host_cores() // world))
@@ -425,7 +444,7 @@ def run_b200(args, name, wl):
     line = {"metric": "reads_per_sec", "value": value, "unit": "reads/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ra["total_ms"] / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64",
             "data": "synthetic", "config": shared_config(name, wl),
-            "details": {"filter_partitioned": partitioned, "reads_per_step_per_gpu": R,
+            "details": {"filter_partitioned": partitioned, "partition_check": part_check, "reads_per_step_per_gpu": R,
                         "filter_rows": int(info.bin_size), "filter_bytes_hbm": int(info.filter_bytes), "row_bits": int(info.row_bits),
                         "minimisers_per_step_per_gpu": minimisers, "classified_frac": float((res["call"] != 255).mean()),
                         "hbm_resident_bases": "2 bits per base (CG_BASES_2BIT), every read on a 64-base boundary",

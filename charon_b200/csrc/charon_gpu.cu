@@ -184,7 +184,8 @@ cgk::CountParams make_params(cg_handle *h) {
     P.n_parts = h->n_parts; P.my_part = h->my_part; P.rows_per_part = h->rows_per_part; P.packed = uint32_t(h->staged_format);
     P.n_exc = h->staged_n_exc; P.exc_pos = h->exc_pos.as<unsigned long long>(); P.exc_seg_off = h->exc_seg_off.as<uint32_t>();
     P.async_gather = h->async_gather_mode < 0 ? (h->filter_bytes > ASYNC_GATHER_MIN_FILTER ? 1 : 0) : uint32_t(h->async_gather_mode);
-    if (h->hash_funs != 3 || h->n_parts || h->mode != 0) P.async_gather = 0;   // the cp.async carrier exists for the deferred-gather case only
+    if (h->n_parts && h->async_gather_mode < 0) P.async_gather = 1;             // rows in peer partitions: the NVLink round trip wants the asynchronous carrier
+    if (h->hash_funs != 3 || h->mode != 0) P.async_gather = 0;                  // the cp.async carrier exists for 3 hash functions on narrow rows only
     for (int i = 0; i < CG_MAX_PARTS; ++i) P.part_base[i] = h->part_base[i];
     return P;
 }

@@ -164,29 +164,37 @@ __device__ __forceinline__ Mask<ModeTraits<MODE>::NW> fetch_row(const void *filt
 }
 
 // Partitioned filter: rows owned by other GPUs are read through their NVLink peer mappings.  Kept out of line so that
-// the replicated hot path keeps its register allocation.
+// the replicated hot path keeps its register allocation.  bulk_contains is an AND over the hash rows (include/index.hpp:
+// 110-112), so the rows this GPU owns are fetched first and a remote row is only requested while some bin is still alive:
+// a k-mer broken by a read error usually dies on its first row, and every request that is not made is one NVLink round trip
+// (the remote 4-byte gathers are request-bound).
 template <int MODE>
 __device__ __noinline__ Mask<ModeTraits<MODE>::NW> bulk_contains_partitioned(const CountParams &P, uint64_t value, uint64_t pol) {
     constexpr int NW = ModeTraits<MODE>::NW;
     Mask<NW> acc;
 #pragma unroll
     for (int j = 0; j < NW; ++j) acc.w[j] = ~uint64_t(0);
-    Mask<NW> r[5];
+    uint32_t owner[5], local[5];
 #pragma unroll
     for (int i = 0; i < 5; ++i)
         if (i < int(P.hash_funs)) {
             const uint32_t row = uint32_t(ibf_row(value, c_ibf_seeds[i], P.hash_shift, P.bin_size));   // rows < 2^32
-            const uint32_t owner = row / P.rows_per_part;
-            const uint64_t local = row - owner * P.rows_per_part;
-            if (owner == P.my_part) r[i] = fetch_row<MODE>(P.filter, local, P.row_shift, pol);
-            else r[i] = fetch_row_remote<MODE>(P.part_base[owner], local, P.row_shift);
+            owner[i] = row / P.rows_per_part;
+            local[i] = row - owner[i] * P.rows_per_part;
         }
+    bool alive = true;
 #pragma unroll
-    for (int i = 0; i < 5; ++i)
-        if (i < int(P.hash_funs)) {
+    for (int pass = 0; pass < 2; ++pass) {          // pass 0: rows in this GPU's own partition; pass 1: the others, one at a time
 #pragma unroll
-            for (int j = 0; j < NW; ++j) acc.w[j] &= r[i].w[j];
-        }
+        for (int i = 0; i < 5; ++i)
+            if (i < int(P.hash_funs) && alive && (owner[i] == P.my_part) == (pass == 0)) {
+                const Mask<NW> r = pass == 0 ? fetch_row<MODE>(P.filter, local[i], P.row_shift, pol) : fetch_row_remote<MODE>(P.part_base[owner[i]], local[i], P.row_shift);
+                uint64_t any = 0;
+#pragma unroll
+                for (int j = 0; j < NW; ++j) { acc.w[j] &= r.w[j]; any |= acc.w[j]; }
+                alive = any != 0;
+            }
+    }
     return acc;
 }
 

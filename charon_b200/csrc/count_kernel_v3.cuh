@@ -218,7 +218,7 @@ count_kernel_v3(const __grid_constant__ CountParams P) {
             constexpr bool ag = AG && (MODE == 0);
             uint32_t dq_w[(DQ && !ag) ? DQ : 1][3], dq_sh[(DQ && !ag) ? DQ : 1];
             uint32_t ndq = 0;
-            const bool can_defer = DQ && P.hash_funs == 3 && P.n_parts == 0;
+            const bool can_defer = DQ && P.hash_funs == 3 && (ag || P.n_parts == 0);   // the cp.async carrier also reaches rows in peer partitions
             auto dq_finish = [&]() {   // register carrier: consume the rows fetched at the end of the previous tile
                 if (DQ && !ag) {
                     const uint32_t rb = 1u << P.row_shift;
@@ -245,6 +245,20 @@ count_kernel_v3(const __grid_constant__ CountParams P) {
             // The values of a stage-0 cohort stay in the ring (behind its head) until its rows 1, 2 have been derived.
             uint32_t s0_n = 0, s1_n = 0, s0_base = 0, s0_span = 0;         // warp-uniform: groups per stage; ring index of the stage-0 cohort's first value and how far the head has moved past it
             uint32_t s0_sh[DQA ? DQA : 1], s1_sh[DQA ? DQA : 1], s1_m0[DQA ? DQA : 1];
+            // 16-byte chunk that holds a row's word, and the row's word / bit position inside it.  Row-range partitioned filter
+            // (SURVEY 8e): the chunk lives in the partition of the GPU that owns the row — this GPU's own memory or a peer's,
+            // mapped over NVLink; the asynchronous copy hides the round trip behind the next tile's hashing either way.
+            auto row_chunk = [&](uint32_t row, uint32_t &word, uint32_t &bitpos) -> const uint32_t * {
+                const uint32_t *base = reinterpret_cast<const uint32_t *>(P.filter);
+                if (P.n_parts) {
+                    const uint32_t owner = row / P.rows_per_part;
+                    row -= owner * P.rows_per_part;
+                    if (owner != P.my_part) base = reinterpret_cast<const uint32_t *>(P.part_base[owner]);
+                }
+                word = row >> (5u - P.row_shift);
+                bitpos = (row << P.row_shift) & 31u;
+                return base + (word & ~3u);
+            };
             auto ag_step = [&](bool bases_group_behind, uint32_t new_groups) {
                 if (ag) {
                     const uint32_t rb = 1u << P.row_shift;
@@ -279,12 +293,12 @@ count_kernel_v3(const __grid_constant__ CountParams P) {
                                 const uint64_t value = ring[(s0_base + uint32_t(g) * 32u + lane) & uint32_t(WLIST_CAP - 1)];
 #pragma unroll
                                 for (int i = 1; i < 3; ++i) {
-                                    const uint32_t row = ibf_row32(value, c_ibf_seeds[i], P.hash_shift, uint32_t(P.bin_size));
-                                    const uint32_t word = row >> (5u - P.row_shift);
+                                    uint32_t word, bitpos;
+                                    const uint32_t *src = row_chunk(ibf_row32(value, c_ibf_seeds[i], P.hash_shift, uint32_t(P.bin_size)), word, bitpos);
                                     asm volatile("cp.async.cg.shared.global.L2::cache_hint [%0], [%1], 16, %2;" ::"r"(gq_s + uint32_t(g * 3 + i) * 512u),
-                                                 "l"(reinterpret_cast<const uint32_t *>(P.filter) + (word & ~3u)), "l"(pol_filter)
+                                                 "l"(src), "l"(pol_filter)
                                                  : "memory");
-                                    sh |= (((row << P.row_shift) & 31u) << (5 * (i - 1))) | ((word & 3u) << (10 + 2 * (i - 1)));
+                                    sh |= (bitpos << (5 * (i - 1))) | ((word & 3u) << (10 + 2 * (i - 1)));
                                 }
                             }
                             s1_sh[g] = sh; s1_m0[g] = m0;
@@ -295,12 +309,12 @@ count_kernel_v3(const __grid_constant__ CountParams P) {
                     for (int g = 0; g < DQA; ++g)
                         if (uint32_t(g) < new_groups) {
                             const uint64_t value = LI(g * 32 + lane);
-                            const uint32_t row = ibf_row32(value, c_ibf_seeds[0], P.hash_shift, uint32_t(P.bin_size));
-                            const uint32_t word = row >> (5u - P.row_shift);
+                            uint32_t word, bitpos;
+                            const uint32_t *src = row_chunk(ibf_row32(value, c_ibf_seeds[0], P.hash_shift, uint32_t(P.bin_size)), word, bitpos);
                             asm volatile("cp.async.cg.shared.global.L2::cache_hint [%0], [%1], 16, %2;" ::"r"(gq_s + uint32_t(g * 3) * 512u),
-                                         "l"(reinterpret_cast<const uint32_t *>(P.filter) + (word & ~3u)), "l"(pol_filter)
+                                         "l"(src), "l"(pol_filter)
                                          : "memory");
-                            s0_sh[g] = ((row << P.row_shift) & 31u) | ((word & 3u) << 5);
+                            s0_sh[g] = bitpos | ((word & 3u) << 5);
                         }
                     s0_n = new_groups;
                     s0_base = qh;

@@ -151,7 +151,15 @@ public:
         classified_counts_.assign(ncat_, 0);
         if (opt_.is_paired) CH_INFO(log_, "%s files %s and %s", opt_.dehost ? "Dehosting" : "Classifying", opt_.read_file.c_str(), opt_.read_file2.c_str());
         else CH_INFO(log_, "%s file %s", opt_.dehost ? "Dehosting" : "Classifying", opt_.read_file.c_str());
+        const auto t_loop0 = std::chrono::steady_clock::now();
         run_pipeline();
+        {
+            const double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t_loop0).count();
+            unsigned long long n = unclassified_;
+            for (uint64_t c : classified_counts_) n += c;
+            CH_INFO(log_, "Read loop: %llu reads in %.3f s (%.0f reads/s); stage wall times: reader %.3f s, scalars + packing (-t %u) %.3f s, waiting for the GPU %.3f s, writer %.3f s",
+                    n, sec, sec > 0 ? double(n) / sec : 0.0, t_reader_, unsigned(opt_.threads), t_prepare_, t_gpu_wait_, t_writer_);
+        }
         CH_INFO(log_, "Results summary: ");
         for (size_t i = 0; i < ncat_; ++i) CH_INFO(log_, "%s :\t\t%llu", idx_.categories[i].c_str(), (unsigned long long)classified_counts_[i]);
         CH_INFO(log_, "unclassified :\t%llu", (unsigned long long)unclassified_);
