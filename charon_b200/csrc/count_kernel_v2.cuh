@@ -118,8 +118,8 @@ __device__ __forceinline__ bool neq64h(uint64_t a, uint64_t b) {
 #endif
 }
 #ifndef CG_TIE_LEAVING_ONLY
-#define CG_TIE_LEAVING_ONLY 0   // see p2_block.  1 (round 1's last commit) is NOT exact on its own: a fast tile then hands no tracked
-#endif                          // position to the next one (tests/test_tile_seams.py); it needs the seam reconstruction of exact_tile.
+#define CG_TIE_LEAVING_ONLY 1   // see p2_block.  On its own (round 1's last commit) this was NOT exact: a fast tile hands no tracked
+#endif                          // position to the next one; exact_tile now reconstructs it (seam_tracked_position, tests/test_tile_seams.py).
 // Store through a 32-bit shared-space address.  A moving generic pointer costs a 64-bit add next to the address the STS uses;
 // deliberately no "memory" clobber (the window-minimum loads around it must stay free to move): the caller fences once.
 __device__ __forceinline__ void st_shared_u64(uint32_t addr, uint64_t v) { asm volatile("st.shared.u64 [%0], %1;" ::"r"(addr), "l"(v)); }
@@ -302,11 +302,41 @@ __device__ __noinline__ void process_exact(const CountParams &P, const Smem2 &S,
     if (do_unq && pc == 1) atomicAdd(&S.uniq[S.b2c[ub]], 1u);
 }
 
+// Tracked position (tile-local k-mer index) in the context window of a tile that has to be redone exactly although the tile
+// before it went down the fast path and so handed nothing over (its last window = this tile's window 0, which holds its
+// minimum m more than once).  seqan3's tracked element is the rightmost minimum of the window in which the current run of
+// equal window minima STARTED (either the previous one fell out and the window was rescanned, or a strictly smaller newcomer
+// took over — then it is that window's only minimum), and it is still inside this window, otherwise the fast tile would have
+// been flagged when it left (leaving value == window minimum, p2_block).  Hence the run started at most WW - 1 windows ago:
+// the values of the WW - 1 k-mers in front of the tile are recomputed from the bases, the run start ws is the first window,
+// going backwards, whose minimum differs from m, and the answer is the rightmost m at or left of k-mer ws + WW - 1.
+template <int WW>
+__device__ __noinline__ uint32_t seam_tracked_position(const CountParams &P, const Smem2 &S, uint64_t m, uint64_t sbase, uint64_t g0) {
+    uint64_t prev[WW > 1 ? WW - 1 : 1];   // prev[i] = value of tile-local k-mer i - (WW - 1)
+    for (int i = 0; i < WW - 1; ++i) {
+        const uint64_t at = sbase + g0 - uint64_t(WW - 1) + uint64_t(i);
+        uint64_t f = 0, rc = 0;
+        for (uint32_t j = 0; j < P.K; ++j) f = f * 5u + ((P.packed == 2 ? code_at<2>(P, S.lut, at + j) : code_at<0>(P, S.lut, at + j)) & 15u);
+        for (uint32_t j = P.K; j-- > 0;) rc = rc * 5u + ((P.packed == 2 ? code_at<2>(P, S.lut, at + j) : code_at<0>(P, S.lut, at + j)) >> 4);
+        f ^= P.seed; rc ^= P.seed;
+        prev[i] = f < rc ? f : rc;
+    }
+    int ws = -(WW - 1);                   // run start, relative to this tile's window 0
+    for (int d = 1; d <= WW - 1; ++d) {   // window -d = k-mers -d .. WW - 1 - d
+        uint64_t mw = ~0ull;
+        for (int x = -d; x <= WW - 1 - d; ++x) { const uint64_t v = x < 0 ? prev[x + WW - 1] : S.arr[x]; mw = v < mw ? v : mw; }
+        if (mw != m) { ws = 1 - d; break; }
+    }
+    for (int x = ws + WW - 1; x >= 0; --x)
+        if (x < WW && S.arr[x] == m) return uint32_t(x);
+    return 0xFFFFFFFFu;                   // not reached for a window that holds m
+}
+
 // Exact minimiser emission for one tile whose raw values sit in S.arr: per run of equal window minima walk the chain
 // p -> rightmost-argmin(window p+1) (see the file header).  `carry` = tracked position (tile-local) entering the tile.
 template <int MODE, int WW>
 __device__ __noinline__ void exact_tile(const CountParams &P, const Smem2 &S, uint32_t *s_nhash, long long *s_carry_pos, uint32_t *s_carry_valid,
-                                        uint32_t Tw, bool first, long long carry, uint64_t g0, bool do_tot, bool do_unq,
+                                        uint32_t Tw, bool first, long long carry, uint64_t sbase, uint64_t g0, bool do_tot, bool do_unq,
                                         uint32_t t0 = threadIdx.x, uint32_t stride = NT2) {
     for (uint32_t w = t0; w < Tw; w += stride) {
         uint64_t m; uint32_t p;
@@ -316,6 +346,12 @@ __device__ __noinline__ void exact_tile(const CountParams &P, const Smem2 &S, ui
             walk = true;
             if (first) emit = true;
             else if (carry >= 0 && carry < WW && S.arr[carry] == m) p = uint32_t(carry);   // context window: restore, no emission
+            else if (carry < 0) {   // the tile before this one took the fast path: which of several equal minima was being tracked?
+                uint32_t occ = 0;
+#pragma unroll 1
+                for (int j = 0; j < WW; ++j) occ += S.arr[j] == m ? 1u : 0u;
+                if (occ > 1) { const uint32_t q = seam_tracked_position<WW>(P, S, m, sbase, g0); if (q < uint32_t(WW)) p = q; }
+            }
         } else {
             uint64_t mp; uint32_t rp;
             scan_window<WW>(S.arr, w - 1, mp, rp);
@@ -552,7 +588,7 @@ __global__ void __launch_bounds__(NT2, CG_V2_MINB) count_kernel_v2(const __grid_
                         __syncthreads();
                         if (tid == 0) s_carry_valid = 0;     // re-armed by the walker of the run alive at the last window
                         __syncthreads();
-                        { const Smem2 Sx = S; exact_tile<MODE, WW>(P, Sx, &s_nhash, &s_carry_pos, &s_carry_valid, Tw, first, carry, g0, do_tot, do_unq); }
+                        { const Smem2 Sx = S; exact_tile<MODE, WW>(P, Sx, &s_nhash, &s_carry_pos, &s_carry_valid, Tw, first, carry, sbase, g0, do_tot, do_unq); }
                         nl = 0;
                         __syncthreads();
                     } else if (tid == 0) {

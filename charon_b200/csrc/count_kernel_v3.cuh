@@ -517,7 +517,7 @@ count_kernel_v3(const __grid_constant__ CountParams P) {
                         __syncwarp();
                         if (lane == 0) *s_carry_valid = 0;   // re-armed by the walker of the run alive at the last window
                         __syncwarp();
-                        { const Smem2 Sx = S; exact_tile<MODE, WW>(P, Sx, s_nhash, s_carry_pos, s_carry_valid, Tw, first, carry, g0, do_tot, do_unq, lane, 32u); }
+                        { const Smem2 Sx = S; exact_tile<MODE, WW>(P, Sx, s_nhash, s_carry_pos, s_carry_valid, Tw, first, carry, sbase, g0, do_tot, do_unq, lane, 32u); }
                         nl = 0;
                     }
                     __syncwarp();
