@@ -109,6 +109,7 @@ public:
     }
     bool ready() const { return ready_; }
     const std::vector<CategoryModel> &models() const { return models_; }
+    const std::vector<TrainingData> &training() const { return training_; }   // read-only view for tests/training_trace.cpp
 
     void force_ready() {   // :463-473
         for (size_t i = 0; i < models_.size(); ++i) if (!models_[i].ready) train(i);
