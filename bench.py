@@ -358,10 +358,13 @@ def run_b200(args, name, wl):
     def resident_arm(batch):
         gpu._check(Lb.cg_stage_batch(gpu._h, C.byref(batch), C.byref(sc)), "cg_stage_batch")
         gpu._staged_n = R
+        sampler = ClockSampler(local_rank); sampler.start()      # early: with 8 ranks nvidia-smi takes a while to print its first line
         for _ in range(args.warmup):
             gpu.run_staged(True)
+        t_wait = time.time()
+        while not sampler.rows and time.time() - t_wait < 3.0:
+            time.sleep(0.02)
         barrier()
-        sampler = ClockSampler(local_rank); sampler.start(); time.sleep(0.25)
         w0 = time.time()
         gpu.timer_start()
         launches = 0
