@@ -218,6 +218,50 @@ def cpu_baseline(wl, records, rec_bin, seconds_target=15.0, threads=0, stage_spl
     return idx, out, (bases, seg_off, r)
 
 
+def cli_tsv_check(n_reads=10_000):
+    """the product BINARY (`charon_b200/charon dehost`, its own FASTQ parser, scalars, packing,
+    pipeline and TSV printer) against the oracle's restatement of the reference program at -t 1, byte for byte, on the smoke
+    configuration (2 x 5 Mbp index written by the oracle, 10 000 reads of 5 kb in a FASTQ file on tmpfs)."""
+    import re
+    import shutil
+    import tempfile
+    import oracle
+    exe = os.path.join(ROOT, "charon_b200", "charon")
+    if not os.path.exists(exe):
+        return {"unavailable": "charon_b200/charon is not built"}
+    wl = WORKLOADS["smoke"]
+    records, rec_bin = make_refs(wl)
+    idx, _ = oracle_index(wl, records, rec_bin, host_cores())
+    L = wl["read_len"]
+    bases, _, _ = make_reads(wl, records, rec_bin, n_reads, first_index=50_000_000)
+    d = tempfile.mkdtemp(prefix="charon_bench_", dir="/dev/shm" if os.path.isdir("/dev/shm") else None)
+    try:
+        fq = fastq_text(bases, n_reads, L)
+        open(os.path.join(d, "reads.fq"), "wb").write(fq)
+        idx.save(os.path.join(d, "smoke.idx"))
+        idx.run_like_reference(fq, threads=1, tsv_path=os.path.join(d, "oracle.tsv"), opts=oracle_options(wl))
+        t0 = time.time()
+        r = subprocess.run([exe, "dehost", os.path.join(d, "reads.fq"), "--db", os.path.join(d, "smoke.idx"), "-t", str(min(host_cores(), 255)),
+                            "--log", os.path.join(d, "charon.log")], stdout=open(os.path.join(d, "gpu.tsv"), "wb"), stderr=subprocess.PIPE, timeout=600)
+        wall = time.time() - t0
+        same = r.returncode == 0 and open(os.path.join(d, "gpu.tsv"), "rb").read() == open(os.path.join(d, "oracle.tsv"), "rb").read()
+        out = {"workload": wl["desc"], "reads": n_reads, "tsv_identical_to_oracle_t1": bool(same), "charon_dehost_wall_s": round(wall, 2),
+               "threads": min(host_cores(), 255), "rows": sum(1 for _ in open(os.path.join(d, "gpu.tsv"), "rb"))}
+        try:
+            m = re.search(r"Read loop: (\d+) reads in ([0-9.]+) s \(([0-9.]+) reads/s\); stage wall times: reader ([0-9.]+) s, scalars \+ packing \(-t \d+\) ([0-9.]+) s, "
+                          r"waiting for the GPU ([0-9.]+) s, writer ([0-9.]+) s", open(os.path.join(d, "charon.log")).read())
+            if m:
+                out.update(read_loop_s=float(m.group(2)), read_loop_reads_per_s=float(m.group(3)), reader_s=float(m.group(4)),
+                           scalars_and_packing_s=float(m.group(5)), waiting_for_gpu_s=float(m.group(6)), writer_s=float(m.group(7)))
+        except Exception:
+            pass
+        if not same:
+            out["stderr_tail"] = r.stderr.decode(errors="replace")[-300:]
+        return out
+    finally:
+        shutil.rmtree(d, ignore_errors=True)
+
+
 def parity_mismatch(g, o, keys=("num_hashes", "counts", "unique_counts", "confidence", "call")):
     """None when every integer output agrees, else a description of the first differing read."""
     for key in keys:
@@ -520,6 +564,11 @@ def run_b200(args, name, wl):
             line["cpu_baseline"] = cb
         else:
             line["parity_on_sample"] = {"ok": bad is None, "reads": n, "rank": 0}
+        if world == 1 and bad is None and not partitioned:
+            gpu.sync()
+            line["cli_tsv_check"] = cli_tsv_check()
+            if line["cli_tsv_check"].get("tsv_identical_to_oracle_t1") is False:
+                bad = "the TSV of charon_b200/charon dehost differs from the oracle's on the smoke configuration: " + json.dumps(line["cli_tsv_check"])
         if bad is not None:
             sys.stderr.write(f"bench.py: PARITY FAILURE against the oracle on {n} reads of the workload: {bad}\n"
                              "bench.py: no bench line is printed for a kernel that is not bit-exact\n")
