@@ -63,10 +63,12 @@ class Info(C.Structure):
                 ("last_d2h_ms", f32), ("last_h2d_bytes", u64), ("last_pack_ms", f32), ("last_packed", u32)]
 
 
+EVAL_STATIC_MAX_READS, EVAL_STATIC_MAX_PAIRS = 16384, 65536    # include/charon_gpu.h
+
 EXPORTS = ["cg_create", "cg_build_index", "cg_destroy", "cg_last_error", "cg_set_stream", "cg_sync", "cg_set_model", "cg_count_batch", "cg_eval_batch",
            "cg_classify_batch", "cg_stage_batch", "cg_run_staged", "cg_fetch_staged", "cg_get_info", "cg_host_alloc", "cg_host_free", "cg_timer_start", "cg_timer_stop", "cg_debug_minimisers",
            "cg_debug_query", "cg_debug_dump_filter", "cg_debug_force_generic", "cg_create_partitioned", "cg_partition_from_replicated",
-           "cg_partition_export", "cg_partition_attach_ipc", "cg_partition_attach_peer", "cg_bench_gather", "cg_submit_batch", "cg_wait_batch", "cg_export_sd_vector", "cg_select_slot", "cg_set_host_pack", "cg_pack_bases", "cg_pack_bases_2bit"]
+           "cg_partition_export", "cg_partition_attach_ipc", "cg_partition_attach_peer", "cg_bench_gather", "cg_submit_batch", "cg_wait_batch", "cg_export_sd_vector", "cg_select_slot", "cg_set_host_pack", "cg_pack_bases", "cg_pack_bases_2bit", "cg_eval_batch_static"]
 
 _lib = None
 
@@ -103,6 +105,7 @@ def load_library():
     L.cg_set_model.argtypes = [vp, P(CategoryModel), P(Thresholds), i32]
     L.cg_count_batch.argtypes = [vp, P(Batch), P(CountsOut)]
     L.cg_eval_batch.argtypes = [vp, u32, vp, vp, vp, P(ReadScalars), P(CallsOut)]
+    L.cg_eval_batch_static.argtypes = [vp, u32, vp, vp, vp, P(ReadScalars), P(CallsOut)]
     L.cg_classify_batch.argtypes = [vp, P(Batch), P(ReadScalars), P(CountsOut), P(CallsOut)]
     L.cg_stage_batch.argtypes = [vp, P(Batch), P(ReadScalars)]
     L.cg_run_staged.argtypes = [vp, i32]
@@ -439,14 +442,20 @@ class GpuClassifier:
         self._check(self._L.cg_wait_batch(self._h, slot), "cg_wait_batch")
         return self._inflight.pop(slot)[-1] if getattr(self, "_inflight", {}).get(slot) else None
 
-    def eval_batch(self, num_hashes, counts, unique_counts, mean_q, compression, length):
+    def eval_batch(self, num_hashes, counts, unique_counts, mean_q, compression, length, static=False):
         n = len(num_hashes)
         nh = np.ascontiguousarray(num_hashes, np.uint32); ct = np.ascontiguousarray(counts, np.uint32); uq = np.ascontiguousarray(unique_counts, np.uint32)
         sc, keep2 = self._scalars(n, mean_q, compression, length)
         res = dict(prob=np.zeros((n, self.ncat), np.float64), call=np.zeros(n, np.uint8), confidence=np.zeros(n, np.uint8))
         ca = CallsOut(res["prob"].ctypes.data, res["call"].ctypes.data, res["confidence"].ctypes.data)
-        self._check(self._L.cg_eval_batch(self._h, n, nh.ctypes.data, ct.ctypes.data, uq.ctypes.data, C.byref(sc), C.byref(ca)), "cg_eval_batch")
+        entry = self._L.cg_eval_batch_static if static else self._L.cg_eval_batch
+        self._check(entry(self._h, n, nh.ctypes.data, ct.ctypes.data, uq.ctypes.data, C.byref(sc), C.byref(ca)), "cg_eval_batch_static" if static else "cg_eval_batch")
         return res
+
+    def eval_batch_static(self, num_hashes, counts, unique_counts, mean_q, compression, length):
+        """cg_eval_batch_static: the same results from the library's static device scratch, no allocation inside the call
+        (at most EVAL_STATIC_MAX_READS reads and EVAL_STATIC_MAX_PAIRS read-category pairs; not in the reference)."""
+        return self.eval_batch(num_hashes, counts, unique_counts, mean_q, compression, length, static=True)
 
     # staged path (device-resident inputs) -----------------------------------------------------------------------
     def stage(self, bases, seg_off, mean_q=None, compression=None, length=None, read_seg=None):

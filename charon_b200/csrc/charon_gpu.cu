@@ -16,6 +16,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -559,3 +560,89 @@ int fetch(cg_handle *h, const cg_counts_out *co, const cg_calls_out *ca) {
 }  // namespace
 
 #include "charon_gpu_api.inc"
+
+// ---- cg_eval_batch_static: the model/call kernels with NO allocation inside the call ------------------------------------
+// No counterpart in the reference; added for callers that may not call cudaMalloc
+// (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  prob_kernel writes the per-(read,
+// category) probabilities that call_kernel reads back: that scratch, and the device copies of the inputs and outputs,
+// live in ONE file-scope device array of CG_EVAL_STATIC_BYTES instead of the handle's cudaMalloc'd buffers.  Every GPU
+// that loads this library holds the array until the process exits.  All calls (and all handles) on a device share it and
+// it keeps the previous call's contents; two calls that overlap on the GPU race.
+namespace {
+
+constexpr size_t ES_READS = CG_EVAL_STATIC_MAX_READS, ES_PAIRS = CG_EVAL_STATIC_MAX_PAIRS;
+// fixed layout, every part a multiple of 256 bytes
+constexpr size_t ES_OFF_NH = 0, ES_OFF_MQ = ES_OFF_NH + ES_READS * 4, ES_OFF_CR = ES_OFF_MQ + ES_READS * 4, ES_OFF_LEN = ES_OFF_CR + ES_READS * 4,
+                 ES_OFF_CNT = ES_OFF_LEN + ES_READS * 4, ES_OFF_UNQ = ES_OFF_CNT + ES_PAIRS * 4, ES_OFF_PROB = ES_OFF_UNQ + ES_PAIRS * 4,
+                 ES_OFF_CALL = ES_OFF_PROB + ES_PAIRS * 8, ES_OFF_CONF = ES_OFF_CALL + ES_READS, ES_TOTAL = ES_OFF_CONF + ES_READS;
+static_assert(ES_TOTAL == CG_EVAL_STATIC_BYTES, "include/charon_gpu.h states the size of the static scratch");
+static_assert(ES_READS % 256 == 0 && ES_PAIRS % 256 == 0, "parts of the static scratch stay 256-byte aligned");
+
+static __device__ __align__(256) unsigned char g_eval_static[CG_EVAL_STATIC_BYTES];
+
+// In host code `g_eval_static` is only a stand-in for the symbol: the device address is looked up once per device, with
+// that device current, and cached here.
+constexpr int ES_MAX_DEVICES = 64;
+unsigned char *g_eval_static_ptr[ES_MAX_DEVICES] = {};
+std::mutex g_eval_static_mx;
+
+int eval_static_address(cg_handle *h, unsigned char **out) {
+    if (h->device < 0 || h->device >= ES_MAX_DEVICES) return fail(h, CG_ERR_ARG, "cg_eval_batch_static: device %d out of range", h->device);
+    std::lock_guard<std::mutex> lk(g_eval_static_mx);
+    if (!g_eval_static_ptr[h->device]) {
+        void *p = nullptr;
+        CU(h, cudaSetDevice(h->device));
+        CU(h, cudaGetSymbolAddress(&p, g_eval_static));
+        if (!p) return fail(h, CG_ERR_CUDA, "cudaGetSymbolAddress(g_eval_static) returned a null address");
+        g_eval_static_ptr[h->device] = static_cast<unsigned char *>(p);
+    }
+    *out = g_eval_static_ptr[h->device];
+    return 0;
+}
+
+}  // namespace
+
+extern "C" int cg_eval_batch_static(cg_handle *h, uint32_t n, const uint32_t *nh, const uint32_t *cnt, const uint32_t *uq,
+                                    const cg_read_scalars *sc, const cg_calls_out *out) {
+    if (!h) return CG_ERR_ARG;
+    if (!h->model_set) return fail(h, CG_ERR_STATE, "cg_set_model must be called before cg_eval_batch_static");
+    const size_t nc = h->ncat, pairs = size_t(n) * nc;
+    if (n > ES_READS || pairs > ES_PAIRS)
+        return fail(h, CG_ERR_ARG, "cg_eval_batch_static: %u reads x %zu categories exceed the static scratch (at most %zu reads and %zu read-category "
+                    "pairs per call); split the batch or use cg_eval_batch", n, nc, ES_READS, ES_PAIRS);
+    unsigned char *S = nullptr;
+    int rc = eval_static_address(h, &S);       // also what a set-up call with n_reads == 0 is for
+    if (rc) return rc;
+    if (n == 0) return 0;
+    if (!nh || !cnt || !uq || !sc || !sc->mean_quality || !sc->compression || !sc->length || !out) return fail(h, CG_ERR_ARG, "null argument");
+    CU(h, cudaSetDevice(h->device));
+    CU(h, cudaMemcpyAsync(S + ES_OFF_NH, nh, size_t(n) * 4, cudaMemcpyHostToDevice, h->stream));
+    CU(h, cudaMemcpyAsync(S + ES_OFF_CNT, cnt, pairs * 4, cudaMemcpyHostToDevice, h->stream));
+    CU(h, cudaMemcpyAsync(S + ES_OFF_UNQ, uq, pairs * 4, cudaMemcpyHostToDevice, h->stream));
+    CU(h, cudaMemcpyAsync(S + ES_OFF_MQ, sc->mean_quality, size_t(n) * 4, cudaMemcpyHostToDevice, h->stream));
+    CU(h, cudaMemcpyAsync(S + ES_OFF_CR, sc->compression, size_t(n) * 4, cudaMemcpyHostToDevice, h->stream));
+    CU(h, cudaMemcpyAsync(S + ES_OFF_LEN, sc->length, size_t(n) * 4, cudaMemcpyHostToDevice, h->stream));
+    // the array still holds the previous call's probabilities and calls: both kernels overwrite every element of this call's
+    // range, and the range is cleared first so that nothing stale can be read back should a launch fail
+    CU(h, cudaMemsetAsync(S + ES_OFF_PROB, 0, pairs * 8, h->stream));
+    CU(h, cudaMemsetAsync(S + ES_OFF_CALL, 0xFF, n, h->stream));
+    CU(h, cudaMemsetAsync(S + ES_OFF_CONF, 0, n, h->stream));
+    cgk::EvalParams E = make_eval(h, n);       // model tables and thresholds of the handle (allocated by cg_set_model)
+    E.num_hashes = reinterpret_cast<const uint32_t *>(S + ES_OFF_NH);
+    E.counts = reinterpret_cast<const uint32_t *>(S + ES_OFF_CNT);
+    E.unique_counts = reinterpret_cast<const uint32_t *>(S + ES_OFF_UNQ);
+    E.mean_quality = reinterpret_cast<const float *>(S + ES_OFF_MQ);
+    E.compression = reinterpret_cast<const float *>(S + ES_OFF_CR);
+    E.length = reinterpret_cast<const uint32_t *>(S + ES_OFF_LEN);
+    E.prob = reinterpret_cast<double *>(S + ES_OFF_PROB);
+    E.call = S + ES_OFF_CALL;
+    E.confidence = S + ES_OFF_CONF;
+    cgk::prob_kernel<<<unsigned((pairs + 127) / 128), 128, 0, h->stream>>>(E);
+    cgk::call_kernel<<<(n + 127) / 128, 128, 0, h->stream>>>(E);
+    CU(h, cudaGetLastError());
+    if (out->probabilities) CU(h, cudaMemcpyAsync(out->probabilities, S + ES_OFF_PROB, pairs * 8, cudaMemcpyDeviceToHost, h->stream));
+    if (out->call) CU(h, cudaMemcpyAsync(out->call, S + ES_OFF_CALL, n, cudaMemcpyDeviceToHost, h->stream));
+    if (out->confidence) CU(h, cudaMemcpyAsync(out->confidence, S + ES_OFF_CONF, n, cudaMemcpyDeviceToHost, h->stream));
+    CU(h, cudaStreamSynchronize(h->stream));
+    return 0;
+}

@@ -209,6 +209,20 @@ int cg_eval_batch(cg_handle *h, uint32_t n_reads, const uint32_t *num_hashes, co
 /* count + eval fused (model fixed up front: the default no---extract invocation). */
 int cg_classify_batch(cg_handle *h, const cg_batch *batch, const cg_read_scalars *scalars,
                       const cg_counts_out *counts_out, const cg_calls_out *calls_out);
+/* cg_eval_batch for callers that may not allocate.  NO counterpart in the reference: added
+ * (code under CUDA graph capture, tight serving loops and harnesses that forbid cudaMalloc).  Same arguments and
+ * results as cg_eval_batch, but the call makes no cudaMalloc / cudaFree: the probabilities the model kernel hands to the
+ * call kernel, and the device copies of inputs and outputs, live in one static device array of CG_EVAL_STATIC_BYTES
+ * (1 343 488 bytes, held by every GPU that loads the library until the process exits).  Limits per call: n_reads <=
+ * CG_EVAL_STATIC_MAX_READS and n_reads * categories <= CG_EVAL_STATIC_MAX_PAIRS; beyond them CG_ERR_ARG with the limits in
+ * cg_last_error.  The array is shared by all handles of a device and keeps the last call's contents (this call's output
+ * range is cleared first): calls that overlap on the GPU — two streams, two threads — race; serialise them.  The first
+ * call on a device resolves the array's device address (cudaGetSymbolAddress): call once with n_reads == 0 at set-up. */
+#define CG_EVAL_STATIC_MAX_READS 16384u
+#define CG_EVAL_STATIC_MAX_PAIRS 65536u
+#define CG_EVAL_STATIC_BYTES (CG_EVAL_STATIC_MAX_READS * 18u + CG_EVAL_STATIC_MAX_PAIRS * 16u)
+int cg_eval_batch_static(cg_handle *h, uint32_t n_reads, const uint32_t *num_hashes, const uint32_t *counts,
+                         const uint32_t *unique_counts, const cg_read_scalars *scalars, const cg_calls_out *out);
 
 /* ---- two-slot pipeline over the same path: cg_submit_batch enqueues H2D + kernels + D2H of one batch on the slot's
  * own stream and returns; cg_wait_batch blocks until that slot's outputs are in the caller's buffers.  With slots 0/1
