@@ -188,6 +188,21 @@ cgk::CountParams make_params(cg_handle *h) {
     if (h->n_parts && h->async_gather_mode < 0) P.async_gather = 1;             // rows in peer partitions: the NVLink round trip wants the asynchronous carrier
     if (h->hash_funs != 3 || h->mode != 0) P.async_gather = 0;                  // the cp.async carrier exists for 3 hash functions on narrow rows only
     for (int i = 0; i < CG_MAX_PARTS; ++i) P.part_base[i] = h->part_base[i];
+    // bins of categories that own several bins; parking pays while they are few (CHARON_ONE_PASS=0 switches it off)
+    P.amb_mode = 0;
+    for (int j = 0; j < 4; ++j) { P.multibin[j] = 0; P.static_best[j] = 0; }
+    if (!h->single_pass && h->bins > 4) {
+        uint32_t per_cat[256] = {};
+        for (uint32_t b = 0; b < h->bins; ++b) ++per_cat[h->h_bin_to_cat[b]];
+        uint32_t multi = 0;
+        for (uint32_t b = 0; b < h->bins; ++b) {
+            if (per_cat[h->h_bin_to_cat[b]] > 1) { P.multibin[b >> 6] |= 1ull << (b & 63u); ++multi; }
+            else P.static_best[b >> 6] |= 1ull << (b & 63u);
+        }
+        const char *ope = std::getenv("CHARON_ONE_PASS");
+        const int one_pass_env = ope ? std::atoi(ope) : -1;
+        P.amb_mode = one_pass_env >= 0 ? uint32_t(one_pass_env != 0) : uint32_t(multi * 8 <= h->bins);
+    }
     return P;
 }
 

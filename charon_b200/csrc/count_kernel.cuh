@@ -61,6 +61,14 @@ struct CountParams {
     const uint32_t *exc_seg_off;
     unsigned long long n_exc;
     const void *part_base[CG_MAX_PARTS];
+    // One-pass counting for indexes where only a few bins belong to categories that own several bins (warp-per-read kernel,
+    // more than 4 bins).  ReadEntry::get_counts needs, per category, the bin with the most hits before it can tell which
+    // hits are unique; a category with ONE bin has no choice to make, so its bin is in the best-bin mask from the start
+    // (`static_best`), and only the minimisers that hit a bin of a multi-bin category (`multibin`) have to wait for the end
+    // of the read: their masks are parked in shared memory and resolved then.  A read that parks more masks than fit is
+    // redone the two-pass way.
+    uint32_t amb_mode;
+    unsigned long long multibin[4], static_best[4];
 };
 
 __constant__ uint64_t c_ibf_seeds[5] = {13572355802537770549ULL, 13043817825332782213ULL, 10650232656628343401ULL,

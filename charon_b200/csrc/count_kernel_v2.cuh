@@ -57,6 +57,10 @@ struct Smem2 {
     unsigned long long *best, *bestmask;
     uint8_t *codes;     // 32 bytes of left slack + NB + slack ; codes[i] for tile base i lives at codes[32 + i]
     uint8_t *lut, *b2c;
+    // one-pass counting (CountParams::amb_mode, warp-per-read kernel only): parked masks of minimisers that hit a bin of a
+    // multi-bin category, amb_cap of them; *amb_n counts every attempt, so amb_n > amb_cap = overflow.  nullptr elsewhere.
+    unsigned long long *amb;
+    uint32_t *amb_n, amb_cap;
 };
 
 template <int KK, int WW>
@@ -73,6 +77,7 @@ __device__ __forceinline__ Smem2 carve2(unsigned char *raw) {
     s.lut = reinterpret_cast<uint8_t *>(s.uniq + 256);
     s.b2c = s.lut + 256;
     s.codes = s.b2c + 256;
+    s.amb = nullptr; s.amb_n = nullptr; s.amb_cap = 0;
     return s;
 }
 
@@ -185,6 +190,22 @@ __device__ __noinline__ uint64_t kmer_value_slow(const CountParams &P, const uin
 }
 
 // per-read counters shared by the list phase and the inline (exact path) emission
+// one-pass counting: park the mask if it touches a bin of a multi-bin category (true = parked, or lost to overflow)
+template <int NW>
+__device__ __forceinline__ bool amb_park(const Mask<NW> &m, const unsigned long long *mb, const Smem2 &S) {
+    bool touch = false;
+#pragma unroll
+    for (int j = 0; j < NW; ++j) touch = touch || (m.w[j] & mb[j]) != 0;
+    if (touch) {
+        const uint32_t slot = atomicAdd(S.amb_n, 1u);
+        if (slot < S.amb_cap) {
+#pragma unroll
+            for (int j = 0; j < NW; ++j) S.amb[slot * NW + j] = m.w[j];
+        }
+    }
+    return touch;
+}
+
 template <int MODE>
 struct Tally {
     static constexpr int NW = ModeTraits<MODE>::NW;
@@ -194,7 +215,8 @@ struct Tally {
         for (int b = 0; b < 4; ++b) { rc_cnt[b] = 0; rc_unq[b] = 0; }
     }
     __device__ __forceinline__ void add(const Mask<NW> &m, const unsigned long long *bm, bool small_bins, bool do_tot, bool do_unq,
-                                        const Smem2 &S) {
+                                        const Smem2 &S, const unsigned long long *mb = nullptr) {
+        if (!small_bins && mb && amb_park<NW>(m, mb, S)) do_unq = false;   // its uniqueness is decided at the end of the read
         if (small_bins) {
             const uint32_t m0 = uint32_t(m.w[0]);
             if (do_tot) {
@@ -290,6 +312,7 @@ __device__ __noinline__ void process_exact(const CountParams &P, const Smem2 &S,
     if (do_tot) atomicAdd(s_nhash, 1u);
     if (!P.filter) return;
     const Mask<NW> m = bulk_contains<MODE>(P, hv, l2_policy_evict_last());
+    if (P.amb_mode && S.amb && do_tot && do_unq && amb_park<NW>(m, P.multibin, S)) do_unq = false;   // one-pass counting, pass 0
     int pc = 0, ub = -1;
 #pragma unroll
     for (int j = 0; j < NW; ++j) {

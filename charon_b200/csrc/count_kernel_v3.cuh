@@ -46,6 +46,9 @@ template <bool AG, bool SMALL = true> struct V3Shape {
 #ifndef CG_V3_WLIST_CAP
 #define CG_V3_WLIST_CAP 256
 #endif
+#ifndef CG_V3_AMB_BYTES
+#define CG_V3_AMB_BYTES 1536                       // per warp: 48 parked 256-bit masks (192 of 64 bits)
+#endif
 constexpr int WLIST_CAP = CG_V3_WLIST_CAP;         // emission ring of a warp (power of two; a tile emits ~60 entries, up to two tiles' worth wait in it)
 
 template <int KK, int WW, bool SMALL, bool AG = false> struct V3Cfg {
@@ -58,12 +61,13 @@ template <int KK, int WW, bool SMALL, bool AG = false> struct V3Cfg {
     static constexpr int CODES = ((32 + 16 * NVL * 32 + 64) + 15) / 16 * 16;
     static constexpr int GQ = AG ? CG_V3_DQA * 3 * 32 * 16 : 0;   // landing slots of the asynchronous gathers: 16 bytes per (group, hash function, lane)
     static constexpr int RAW = NVL * 32 * 16;     // cp.async staging of the next tile's bases (ASCII, or 32 rank nibbles per vector)
+    static constexpr int AMB = SMALL ? 0 : CG_V3_AMB_BYTES;   // one-pass counting: parked masks (CountParams::amb_mode)
     static_assert((63 + NB + 31) / 32 <= 32, "packed transports: 32 bases per lane must cover a tile");
     // a lane that overruns its PRIV_CAP slots (such a tile is redone exactly) spills into its right neighbour's slots; lane 31
     // spills into PRIV_GUARD, never into the list, whose head holds minimisers still waiting for a full gather group
     static constexpr int PRIV_GUARD = WW + 1 - PRIV_CAP > 0 ? WW + 1 - PRIV_CAP : 0;
     static constexpr size_t WARP_BYTES = size_t(NK) * 8 + (size_t(32) * PRIV_CAP + PRIV_GUARD) * 8 + size_t(WLIST_CAP) * 8 + size_t(NCNT) * 8 + 32 +
-                                         size_t(NCNT) * 4 * 2 + CODES + RAW + GQ;
+                                         size_t(NCNT) * 4 * 2 + CODES + RAW + GQ + AMB;
     static constexpr size_t SMEM = 512 + V3Shape<AG, SMALL>::WARPS * WARP_BYTES;
     static_assert(SMEM <= 227 * 1024, "a CTA of the warp-per-read kernel must fit the 227 KB of shared memory of an SM");
     static_assert(((size_t(32) * PRIV_CAP + PRIV_GUARD) * 8) % 16 == 0 && CODES % 16 == 0 && WARP_BYTES % 16 == 0,
@@ -101,7 +105,15 @@ count_kernel_v3(const __grid_constant__ CountParams P) {
         S.cnt = reinterpret_cast<uint32_t *>(S.bestmask + 4);
         S.uniq = S.cnt + C::NCNT;
         S.codes = reinterpret_cast<uint8_t *>(S.uniq + C::NCNT);
+        S.amb = SMALL ? nullptr : reinterpret_cast<unsigned long long *>(S.codes + C::CODES + C::RAW + C::GQ);
+        S.amb_cap = uint32_t(C::AMB / (8 * NW));
     }
+    __shared__ uint32_t s_amb_n_w[WARPS3];
+    S.amb_n = &s_amb_n_w[warp];
+    const bool amb_mode = !SMALL && P.amb_mode != 0;
+    unsigned long long mbw[NW];
+#pragma unroll
+    for (int j = 0; j < NW; ++j) mbw[j] = P.multibin[j];
     uint4 *const raw = reinterpret_cast<uint4 *>(S.codes + C::CODES);   // 16-byte aligned: every term of WARP_BYTES is a multiple of 16
     __shared__ uint32_t s_nhash_w[WARPS3], s_carry_valid_w[WARPS3];
     __shared__ long long s_carry_pos_w[WARPS3];
@@ -183,19 +195,22 @@ count_kernel_v3(const __grid_constant__ CountParams P) {
         }
         if (!skip) {
         for (uint32_t i = lane; i < uint32_t(C::NCNT); i += 32) { S.cnt[i] = 0; S.uniq[i] = 0; S.best[i] = 0; }
-        if (lane < 4) S.bestmask[lane] = P.single_pass ? ~0ull : 0ull;
-        if (lane == 0) *s_nhash = 0;
+        if (lane < 4) S.bestmask[lane] = P.single_pass ? ~0ull : (amb_mode ? P.static_best[lane] : 0ull);
+        if (lane == 0) { *s_nhash = 0; *S.amb_n = 0; }
         T.zero();
         __syncwarp();
         const int npass = P.single_pass ? 1 : 2;
         for (int pass = 0; pass < npass; ++pass) {
             const bool do_tot = (pass == 0);
-            const bool do_unq = P.single_pass || pass == 1;
+            // one-pass counting: pass 0 also decides uniqueness wherever no multi-bin category is involved and parks the rest
+            const bool amb_now = amb_mode && pass == 0;
+            const bool do_unq = P.single_pass || pass == 1 || amb_now;
+            const unsigned long long *const mb = amb_now ? mbw : nullptr;
             __syncwarp();
             unsigned long long bm[NW];
 #pragma unroll
             for (int j = 0; j < NW; ++j) bm[j] = S.bestmask[j];
-            const bool last_pass = (pass == npass - 1);
+            const bool last_pass = (pass == npass - 1) || amb_now;   // amb_now: a second pass only after an overflow
 
             // S.list is a ring: `pend` emitted values starting at `qh` wait to be queried (warp-uniform); only full groups of 32 are
             // queried per tile, the rest waits for the next tile's emissions.
@@ -230,7 +245,7 @@ count_kernel_v3(const __grid_constant__ CountParams P) {
 #pragma unroll
                             for (int j = 1; j < NW; ++j) m.w[j] = 0;
                             m.w[0] = ((dq_w[g][0] >> (dq_sh[g] & 31u)) & (dq_w[g][1] >> ((dq_sh[g] >> 5) & 31u)) & (dq_w[g][2] >> ((dq_sh[g] >> 10) & 31u))) & row_msk;
-                            T.add(m, bm, small_bins, do_tot, do_unq, S);
+                            T.add(m, bm, small_bins, do_tot, do_unq, S, mb);
                         }
                 }
                 ndq = 0;
@@ -279,7 +294,7 @@ count_kernel_v3(const __grid_constant__ CountParams P) {
 #pragma unroll
                             for (int j = 1; j < NW; ++j) m.w[j] = 0;
                             m.w[0] = s1_m0[g] & (w1 >> (sh & 31u)) & (w2 >> ((sh >> 5) & 31u));
-                            if (m.w[0]) T.add(m, bm, small_bins, do_tot, do_unq, S);
+                            if (m.w[0]) T.add(m, bm, small_bins, do_tot, do_unq, S, mb);
                         }
                     // stage 0 -> stage 1
 #pragma unroll
@@ -560,7 +575,7 @@ count_kernel_v3(const __grid_constant__ CountParams P) {
                         }
                         for (uint32_t i = first_now + lane; i < fullg; i += 32) {
                             const Mask<NW> m = bulk_contains<MODE>(P, LI(i), pol_filter);
-                            T.add(m, bm, small_bins, do_tot, do_unq, S);
+                            T.add(m, bm, small_bins, do_tot, do_unq, S, mb);
                         }
                         qh = (qh + fullg) & uint32_t(WLIST_CAP - 1);
                         pend = pend + nl - fullg;
@@ -582,7 +597,7 @@ count_kernel_v3(const __grid_constant__ CountParams P) {
                 __syncwarp();
                 for (uint32_t i = lane; i < pend; i += 32) {
                     const Mask<NW> m = bulk_contains<MODE>(P, LI(i), pol_filter);
-                    T.add(m, bm, small_bins, do_tot, do_unq, S);
+                    T.add(m, bm, small_bins, do_tot, do_unq, S, mb);
                 }
                 pend = 0;
             }
@@ -606,6 +621,23 @@ count_kernel_v3(const __grid_constant__ CountParams P) {
                         const uint32_t bb = 255u - uint32_t(S.best[c] & 255ull);
                         if (bb < P.bins) atomicOr(&S.bestmask[bb >> 6], 1ull << (bb & 63u));
                     }
+            }
+            if (amb_now) {   // the best bins are known: decide the parked minimisers, or redo the read's uniqueness in a second pass
+                __syncwarp();
+                const uint32_t na = *S.amb_n;
+                if (na <= S.amb_cap) {
+                    for (uint32_t i = lane; i < na; i += 32) {
+                        int pc = 0, ub = -1;
+#pragma unroll
+                        for (int j = 0; j < NW; ++j) {
+                            const uint64_t y = S.amb[i * NW + j] & S.bestmask[j];
+                            if (y) { pc += __popcll(y); ub = j * 64 + (__ffsll((long long)y) - 1); }
+                        }
+                        if (pc == 1) atomicAdd(&S.uniq[S.b2c[ub]], 1u);
+                    }
+                    break;
+                }
+                for (uint32_t i = lane; i < uint32_t(C::NCNT); i += 32) S.uniq[i] = 0;
             }
         }  // passes
         __syncwarp();
