@@ -564,6 +564,21 @@ int fetch_finish(cg_handle *h) {
     if (cudaEventElapsedTime(&ms, h->ev[2], h->ev[3]) == cudaSuccess) h->info.last_count_kernel_ms = ms;
     if (cudaEventElapsedTime(&ms, h->ev[3], h->ev[4]) == cudaSuccess) h->info.last_eval_kernel_ms = ms;
     if (cudaEventElapsedTime(&ms, h->ev[5], h->ev[6]) == cudaSuccess) h->info.last_d2h_ms = ms;
+    // CHARON_TRACE_SLOTS=1: device-side timeline of this batch (ms since the first traced batch's copy began), one line per batch:
+    // where copies and kernels of the two slots really overlap (tools/e2e_probe.py)
+    static const bool trace = std::getenv("CHARON_TRACE_SLOTS") != nullptr;
+    if (trace) {
+        static cudaEvent_t base = nullptr;
+        static std::chrono::steady_clock::time_point hbase;
+        if (!base) {
+            cudaEventCreate(&base); cudaEventRecord(base, h->stream); cudaEventSynchronize(base);
+            hbase = std::chrono::steady_clock::now();
+        }
+        float t[7] = {};
+        for (int i = 0; i < 7; ++i) if (cudaEventElapsedTime(&t[i], base, h->ev[i]) != cudaSuccess) t[i] = -1;
+        std::fprintf(stderr, "[slot %d] wait returned at host %.3f | device: h2d %.3f..%.3f  count %.3f..%.3f  eval ..%.3f  d2h %.3f..%.3f\n", h->active_slot,
+                     std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - hbase).count(), t[0], t[1], t[2], t[3], t[4], t[5], t[6]);
+    }
     cudaGetLastError();
     return 0;
 }
