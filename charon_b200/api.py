@@ -60,7 +60,7 @@ class Info(C.Structure):
     _fields_ = [("bin_size", u64), ("filter_bytes", u64), ("row_bits", u32), ("single_pass", u32), ("sm_count", u32), ("count_grid", u32),
                 ("count_block", u32), ("count_smem_bytes", u32), ("last_minimisers", u64), ("last_bases", u64),
                 ("last_kernel_launches", u32), ("last_count_kernel_ms", f32), ("last_eval_kernel_ms", f32), ("last_h2d_ms", f32),
-                ("last_d2h_ms", f32), ("last_h2d_bytes", u64), ("last_pack_ms", f32), ("last_packed", u32)]
+                ("last_d2h_ms", f32), ("last_h2d_bytes", u64), ("last_pack_ms", f32), ("last_packed", u32), ("last_gzip_kernel_ms", f32)]
 
 
 EVAL_STATIC_MAX_READS, EVAL_STATIC_MAX_PAIRS = 16384, 65536    # include/charon_gpu.h
@@ -68,7 +68,7 @@ EVAL_STATIC_MAX_READS, EVAL_STATIC_MAX_PAIRS = 16384, 65536    # include/charon_
 EXPORTS = ["cg_create", "cg_build_index", "cg_destroy", "cg_last_error", "cg_set_stream", "cg_sync", "cg_set_model", "cg_count_batch", "cg_eval_batch",
            "cg_classify_batch", "cg_stage_batch", "cg_run_staged", "cg_fetch_staged", "cg_get_info", "cg_host_alloc", "cg_host_free", "cg_timer_start", "cg_timer_stop", "cg_debug_minimisers",
            "cg_debug_query", "cg_debug_dump_filter", "cg_debug_force_generic", "cg_create_partitioned", "cg_partition_from_replicated",
-           "cg_partition_export", "cg_partition_attach_ipc", "cg_partition_attach_peer", "cg_bench_gather", "cg_submit_batch", "cg_wait_batch", "cg_export_sd_vector", "cg_select_slot", "cg_set_host_pack", "cg_pack_bases", "cg_pack_bases_2bit", "cg_eval_batch_static"]
+           "cg_partition_export", "cg_partition_attach_ipc", "cg_partition_attach_peer", "cg_bench_gather", "cg_submit_batch", "cg_wait_batch", "cg_export_sd_vector", "cg_select_slot", "cg_set_host_pack", "cg_pack_bases", "cg_pack_bases_2bit", "cg_eval_batch_static", "cg_compression_batch", "cg_fetch_compression"]
 
 _lib = None
 
@@ -105,6 +105,8 @@ def load_library():
     L.cg_set_model.argtypes = [vp, P(CategoryModel), P(Thresholds), i32]
     L.cg_count_batch.argtypes = [vp, P(Batch), P(CountsOut)]
     L.cg_eval_batch.argtypes = [vp, u32, vp, vp, vp, P(ReadScalars), P(CallsOut)]
+    L.cg_compression_batch.argtypes = [vp, P(Batch), vp, vp]
+    L.cg_fetch_compression.argtypes = [vp, i32, vp]
     L.cg_eval_batch_static.argtypes = [vp, u32, vp, vp, vp, P(ReadScalars), P(CallsOut)]
     L.cg_classify_batch.argtypes = [vp, P(Batch), P(ReadScalars), P(CountsOut), P(CallsOut)]
     L.cg_stage_batch.argtypes = [vp, P(Batch), P(ReadScalars)]
@@ -399,10 +401,11 @@ class GpuClassifier:
 
     @staticmethod
     def _scalars(n, mean_q, compression, length):
-        mq = np.ascontiguousarray(mean_q, dtype=np.float32); cr = np.ascontiguousarray(compression, dtype=np.float32)
+        mq = np.ascontiguousarray(mean_q, dtype=np.float32)
+        cr = np.ascontiguousarray(compression, dtype=np.float32) if compression is not None else None    # None: computed on the device
         ln = np.ascontiguousarray(length, dtype=np.uint32)
-        assert len(mq) == n and len(cr) == n and len(ln) == n
-        return ReadScalars(mq.ctypes.data, cr.ctypes.data, ln.ctypes.data), (mq, cr, ln)
+        assert len(mq) == n and (cr is None or len(cr) == n) and len(ln) == n
+        return ReadScalars(mq.ctypes.data, cr.ctypes.data if cr is not None else None, ln.ctypes.data), (mq, cr, ln)
 
     def count_batch(self, bases, seg_off, read_seg=None):
         b, keep, n = self._batch(bases, seg_off, read_seg)
@@ -441,6 +444,18 @@ class GpuClassifier:
     def wait(self, slot):
         self._check(self._L.cg_wait_batch(self._h, slot), "cg_wait_batch")
         return self._inflight.pop(slot)[-1] if getattr(self, "_inflight", {}).get(slot) else None
+
+    def compression_batch(self, bases, seg_off, read_seg=None):
+        """cg_compression_batch: gzip size (zlib level 6, gzip wrapper) and compression ratio of every read, computed on the GPU."""
+        b, keep, n = self._batch(bases, seg_off, read_seg)
+        res = dict(size=np.zeros(n, np.uint32), ratio=np.zeros(n, np.float32))
+        self._check(self._L.cg_compression_batch(self._h, C.byref(b), res["size"].ctypes.data, res["ratio"].ctypes.data), "cg_compression_batch")
+        return res
+
+    def fetch_compression(self, slot, n):
+        out = np.zeros(n, np.float32)
+        self._check(self._L.cg_fetch_compression(self._h, slot, out.ctypes.data), "cg_fetch_compression")
+        return out
 
     def eval_batch(self, num_hashes, counts, unique_counts, mean_q, compression, length, static=False):
         n = len(num_hashes)

@@ -27,6 +27,7 @@
 #include "eval_kernel.cuh"
 #include "filter_build.cuh"
 #include "gather_bench.cuh"
+#include "gzip_size_kernel.cuh"
 
 namespace {
 
@@ -80,6 +81,8 @@ struct cg_handle {
     cg_thresholds thr{};
     // batch buffers
     DevBuf bases, seg_off, read_seg, num_hashes, counts, unique, prob, call, conf, mq, cr, len, counter, dbg, dbgn;
+    DevBuf gz_size, gz_scratch;   // compression-ratio kernel: gzip size per read (per slot), per-warp scratch (shared by the slots: their kernels never overlap)
+    bool staged_device_cr = false;   // the batch came without compression ratios: gzip_size_kernel fills `cr` before the model kernels
     DevBuf seg_len, exc_pos, exc_seg_off, unpack_src;   // optional segment lengths; two-bit transport: exception list + per-segment CSR; packed input of the generic kernel
     uint32_t staged_reads = 0, staged_segs = 0;
     uint64_t staged_bases = 0;
@@ -104,7 +107,8 @@ struct cg_handle {
     struct Parked {
         cudaStream_t stream = nullptr;
         cudaEvent_t ev[8] = {};
-        DevBuf bases, seg_off, read_seg, num_hashes, counts, unique, prob, call, conf, mq, cr, len, counter, seg_len, exc_pos, exc_seg_off, unpack_src;
+        DevBuf bases, seg_off, read_seg, num_hashes, counts, unique, prob, call, conf, mq, cr, len, counter, seg_len, exc_pos, exc_seg_off, unpack_src, gz_size;
+        bool staged_device_cr = false;
         int staged_format = 0; bool staged_has_seg_len = false; uint64_t staged_n_exc = 0;
         uint32_t staged_reads = 0, staged_segs = 0;
         uint64_t staged_bases = 0, staged_max_read_len = 0;
@@ -129,6 +133,7 @@ struct cg_handle {
         std::swap(staged_has_read_seg, parked.staged_has_read_seg); std::swap(staged_has_scalars, parked.staged_has_scalars);
         std::swap(staged_packed, parked.staged_packed); std::swap(pack, parked.pack);
         std::swap(seg_len, parked.seg_len); std::swap(exc_pos, parked.exc_pos); std::swap(exc_seg_off, parked.exc_seg_off); std::swap(unpack_src, parked.unpack_src);
+        std::swap(gz_size, parked.gz_size); std::swap(staged_device_cr, parked.staged_device_cr);
         std::swap(staged_format, parked.staged_format); std::swap(staged_has_seg_len, parked.staged_has_seg_len); std::swap(staged_n_exc, parked.staged_n_exc);
         std::swap(active_pending, parked.pending);
         std::swap(act_co, parked.co); std::swap(act_ca, parked.ca); std::swap(act_has_co, parked.has_co); std::swap(act_has_ca, parked.has_ca);
@@ -502,11 +507,13 @@ int stage(cg_handle *h, const cg_batch *b, const cg_read_scalars *sc) {
     CU(h, cudaMemcpyAsync(h->seg_off.p, b->n_segs ? b->seg_off : zero_off, (size_t(b->n_segs) + 1) * 8, cudaMemcpyHostToDevice, h->stream));
     if (b->read_seg) CU(h, cudaMemcpyAsync(h->read_seg.p, b->read_seg, (size_t(b->n_reads) + 1) * 4, cudaMemcpyHostToDevice, h->stream));
     if (b->seg_len && b->n_segs) CU(h, cudaMemcpyAsync(h->seg_len.p, b->seg_len, size_t(b->n_segs) * 8, cudaMemcpyHostToDevice, h->stream));
-    h->staged_has_scalars = false;
+    h->staged_has_scalars = false; h->staged_device_cr = false;
     if (sc && b->n_reads) {
-        if (!sc->mean_quality || !sc->compression || !sc->length) return fail(h, CG_ERR_ARG, "null read scalars");
+        if (!sc->mean_quality || !sc->length) return fail(h, CG_ERR_ARG, "null read scalars");
         CU(h, cudaMemcpyAsync(h->mq.p, sc->mean_quality, size_t(b->n_reads) * 4, cudaMemcpyHostToDevice, h->stream));
-        CU(h, cudaMemcpyAsync(h->cr.p, sc->compression, size_t(b->n_reads) * 4, cudaMemcpyHostToDevice, h->stream));
+        // compression == NULL: the library computes the ratios on the device (gzip_size_kernel) before the model kernels
+        if (sc->compression) CU(h, cudaMemcpyAsync(h->cr.p, sc->compression, size_t(b->n_reads) * 4, cudaMemcpyHostToDevice, h->stream));
+        h->staged_device_cr = sc->compression == nullptr;
         CU(h, cudaMemcpyAsync(h->len.p, sc->length, size_t(b->n_reads) * 4, cudaMemcpyHostToDevice, h->stream));
         h->staged_has_scalars = true;
     }
@@ -521,8 +528,48 @@ int stage(cg_handle *h, const cg_batch *b, const cg_read_scalars *sc) {
     return 0;
 }
 
+// gzip size (and ratio) of every staged read: one warp per read, per-warp scratch of 5 bytes per base of the longest read
+int launch_gzip(cg_handle *h, float *ratio_out) {
+    const uint32_t n = h->staged_reads;
+    if (!n) return 0;
+    if (h->staged_max_read_len > dsz::DSZ_MAX_LEN)
+        return fail(h, CG_ERR_ARG, "compression ratio on the device: a read of this batch spans %llu bases, the limit is %u (zlib slides its window beyond that): "
+                    "compute the ratios of this batch on the host and pass them in cg_read_scalars", (unsigned long long)h->staged_max_read_len, dsz::DSZ_MAX_LEN);
+    static int blocks_per_sm = 0;
+    if (!blocks_per_sm) {
+        cudaError_t e = cudaFuncSetAttribute(cgk::gzip_size_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(cgk::GZ_SMEM));
+        if (e != cudaSuccess) return fail(h, CG_ERR_CUDA, "gzip_size_kernel attribute: %s", cudaGetErrorString(e));
+        int nb = 0;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, cgk::gzip_size_kernel, cgk::GZ_WARPS * 32, cgk::GZ_SMEM);
+        blocks_per_sm = nb > 0 ? nb : 1;
+    }
+    const uint64_t cap = (std::max<uint64_t>(h->staged_max_read_len, 64) + 63) / 64 * 64;
+    const uint64_t want_blocks = (uint64_t(n) + cgk::GZ_WARPS - 1) / cgk::GZ_WARPS;
+    const unsigned grid = unsigned(std::min<uint64_t>(want_blocks, uint64_t(h->sm_count) * blocks_per_sm));
+    RSV(h, h->gz_scratch, size_t(grid) * cgk::GZ_WARPS * cap * 5);
+    RSV(h, h->gz_size, size_t(n) * 4);
+    cgk::GzParams G{};
+    G.bases = h->bases.as<uint8_t>(); G.format = uint32_t(h->staged_format);
+    G.seg_off = h->seg_off.as<uint64_t>(); G.seg_len = h->staged_has_seg_len ? h->seg_len.as<uint64_t>() : nullptr;
+    G.read_seg = h->staged_has_read_seg ? h->read_seg.as<uint32_t>() : nullptr;
+    G.exc_pos = h->exc_pos.as<unsigned long long>(); G.exc_seg_off = h->exc_seg_off.as<uint32_t>(); G.n_exc = h->staged_n_exc;
+    G.n_reads = n; G.work_counter = h->counter.as<uint32_t>();
+    G.scratch = h->gz_scratch.as<uint8_t>(); G.scratch_stride = cap * 5;
+    G.size_out = h->gz_size.as<uint32_t>(); G.ratio_out = ratio_out;
+    CU(h, cudaMemsetAsync(h->counter.p, 0, 4, h->stream));
+    cgk::gzip_size_kernel<<<grid, cgk::GZ_WARPS * 32, cgk::GZ_SMEM, h->stream>>>(G);
+    CU(h, cudaGetLastError());
+    h->info.last_kernel_launches += 1;
+    return 0;
+}
+
 int run(cg_handle *h, bool with_eval) {
     h->info.last_kernel_launches = 0;
+    if (with_eval && h->staged_device_cr) {
+        CU(h, cudaEventRecord(h->ev[7], h->stream));
+        int rc = launch_gzip(h, h->cr.as<float>());
+        if (rc) return rc;
+    }
     CU(h, cudaEventRecord(h->ev[2], h->stream));
     if (h->timing) CU(h, cudaEventRecord(h->next_tev(), h->stream));
     int rc = launch_count(h, make_params(h));
@@ -564,6 +611,8 @@ int fetch_finish(cg_handle *h) {
     if (cudaEventElapsedTime(&ms, h->ev[2], h->ev[3]) == cudaSuccess) h->info.last_count_kernel_ms = ms;
     if (cudaEventElapsedTime(&ms, h->ev[3], h->ev[4]) == cudaSuccess) h->info.last_eval_kernel_ms = ms;
     if (cudaEventElapsedTime(&ms, h->ev[5], h->ev[6]) == cudaSuccess) h->info.last_d2h_ms = ms;
+    h->info.last_gzip_kernel_ms = 0;
+    if (h->staged_device_cr && cudaEventElapsedTime(&ms, h->ev[7], h->ev[2]) == cudaSuccess) h->info.last_gzip_kernel_ms = ms;
     // CHARON_TRACE_SLOTS=1: device-side timeline of this batch (ms since the first traced batch's copy began), one line per batch:
     // where copies and kernels of the two slots really overlap (tools/e2e_probe.py)
     static const bool trace = std::getenv("CHARON_TRACE_SLOTS") != nullptr;

@@ -242,16 +242,18 @@ DS_HD void tally_dist(Trees &T, uint32_t dist, uint32_t lc) {   // dist = match 
 // A C G T N (the only letters of an uppercase dna5 string) -> 0..4; three letters -> 0..124
 DS_HD uint32_t letter_code(uint8_t c) { return c == 'A' ? 0u : (c == 'C' ? 1u : (c == 'G' ? 2u : (c == 'T' ? 3u : 4u))); }
 
-// The lazy-match state machine of deflate_slow.  M supplies the match search:
+// The lazy-match state machine of deflate_slow.  M supplies the match search, S receives the symbols:
 //   bool M.head(p, q)                          most recent earlier position with the same three letters (false: none)
 //   uint32_t M.longest(p, prev_length, start)  zlib's longest_match at position p (start: in = previous match start, out = new)
 //   uint8_t M.at(p)                            letter at position p
+//   S.lit(c), S.dist(distance, length - 3)     _tr_tally;  uint64_t S.flush(bits, stored_len)  _tr_flush_block
+// (on the device every lane of a warp runs this with identical values; only S decides which lane touches the trees).
 // Returns the size in bytes of the gzip stream.
-template <class M>
-DS_HD uint32_t gzip_size(M &m, Trees &T, uint32_t n) {
+template <class M, class S>
+DS_HD uint32_t gzip_size(M &m, S &sink, uint32_t n) {
     if (n > DSZ_MAX_LEN) return DSZ_UNSUPPORTED;
-    init_block(T);
     uint64_t bits = 0;
+    uint32_t syms = 0;
     uint32_t strstart = 0, block_start = 0, match_length = MIN_MATCH - 1, prev_length = MIN_MATCH - 1, match_start = 0, prev_match = 0;
     bool match_available = false;
     while (strstart < n) {
@@ -262,27 +264,34 @@ DS_HD uint32_t gzip_size(M &m, Trees &T, uint32_t n) {
         match_length = MIN_MATCH - 1;
         if (has_head && prev_length < MAX_LAZY && strstart - hash_head <= MAX_DIST) {
             match_length = m.longest(strstart, prev_length, match_start);
-            if (match_length <= 5 && match_length == uint32_t(MIN_MATCH) && strstart - match_start > TOO_FAR) match_length = MIN_MATCH - 1;
+            if (match_length == uint32_t(MIN_MATCH) && strstart - match_start > TOO_FAR) match_length = MIN_MATCH - 1;
         }
         if (prev_length >= uint32_t(MIN_MATCH) && match_length <= prev_length) {
-            tally_dist(T, strstart - 1 - prev_match, prev_length - MIN_MATCH);
-            const bool bflush = T.syms == SYMS_PER_BLOCK;
+            sink.dist(strstart - 1 - prev_match, prev_length - MIN_MATCH);
             strstart += prev_length - 1;          // the strings in between are inserted by construction (occ[] holds every position)
             match_available = false;
             match_length = MIN_MATCH - 1;
-            if (bflush) { bits = flush_block(T, bits, strstart - block_start, true); block_start = strstart; }
+            if (++syms == SYMS_PER_BLOCK) { bits = sink.flush(bits, strstart - block_start); block_start = strstart; syms = 0; }
         } else if (match_available) {
-            tally_lit(T, m.at(strstart - 1));
-            if (T.syms == SYMS_PER_BLOCK) { bits = flush_block(T, bits, strstart - block_start, true); block_start = strstart; }
+            sink.lit(m.at(strstart - 1));
+            if (++syms == SYMS_PER_BLOCK) { bits = sink.flush(bits, strstart - block_start); block_start = strstart; syms = 0; }
             strstart++;
         } else {
             match_available = true;
             strstart++;
         }
     }
-    if (match_available) tally_lit(T, m.at(strstart - 1));
-    bits = flush_block(T, bits, strstart - block_start, true);     // the last block (Z_FINISH), also for an empty input
+    if (match_available) sink.lit(m.at(strstart - 1));
+    bits = sink.flush(bits, strstart - block_start);     // the last block (Z_FINISH), also for an empty input
     return 10u + uint32_t((bits + 7) >> 3) + 8u;
 }
+
+// the plain sink: one thread owns the trees
+struct TreeSink {
+    Trees &T;
+    DS_HD void lit(uint8_t c) { tally_lit(T, c); }
+    DS_HD void dist(uint32_t d, uint32_t lc) { tally_dist(T, d, lc); }
+    DS_HD uint64_t flush(uint64_t bits, uint32_t stored_len) { return flush_block(T, bits, stored_len, true); }
+};
 
 }  // namespace dsz

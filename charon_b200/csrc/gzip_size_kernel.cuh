@@ -1,0 +1,208 @@
+// charon_b200/csrc/gzip_size_kernel.cuh — the compression-ratio scalar on the device ("compression-ratio computation
+// (the real e2e bottleneck)"; reference src/utils.cpp:114-124 + src/dehost_main.cpp:359-361: ratio = size of gzip::compress(
+// uppercase dna5 string) / length).  deflate_size.cuh holds the algorithm; here: one WARP per read.
+//   1. text: the read's segments, as the uppercase dna5 letters A C G T N, one byte each, in the warp's scratch (global memory);
+//   2. counting sort of the positions by their three-letter code (125 buckets, stable): occ[] = positions bucket by bucket in
+//      ascending order, idx[p] = where p sits in occ[]; a zlib hash chain from p = occ[idx[p] - 1], occ[idx[p] - 2], ...;
+//   3. deflate_slow, every lane running the same state machine; longest_match examines 32 chain candidates per round, one
+//      per lane, and reproduces zlib's sequential rules (strictly longer replaces, stop at nice_length) with a prefix maximum;
+//   4. lane 0 owns the Huffman trees (shared memory) and closes the blocks.
+#pragma once
+#include <cstdint>
+#include "deflate_size.cuh"
+
+namespace cgk {
+
+struct GzParams {
+    const uint8_t *bases;                 // staged batch, device format: 0 ASCII, 2 two bits per base
+    uint32_t format;
+    const uint64_t *seg_off, *seg_len;    // seg_len may be NULL
+    const uint32_t *read_seg;             // may be NULL
+    const unsigned long long *exc_pos; const uint32_t *exc_seg_off; unsigned long long n_exc;
+    uint32_t n_reads;
+    uint32_t *work_counter;
+    uint8_t *scratch; uint64_t scratch_stride;   // per warp: text[cap] | occ u16[cap] | idx u16[cap], cap = scratch_stride / 5
+    uint32_t *size_out;                   // gzip size per read (DSZ_UNSUPPORTED: longer than DSZ_MAX_LEN)
+    float *ratio_out;                     // float(double(size) / double(length)); may be NULL
+};
+
+constexpr int GZ_WARPS = 8;
+
+struct WarpMatcher {
+    const uint8_t *text; const uint16_t *occ, *idx; const uint32_t *start; uint32_t n, lane;
+    __device__ __forceinline__ uint32_t code(uint32_t p) const {
+        return dsz::letter_code(text[p]) * 25u + dsz::letter_code(text[p + 1]) * 5u + dsz::letter_code(text[p + 2]);
+    }
+    __device__ __forceinline__ uint8_t at(uint32_t p) const { return text[p]; }
+    __device__ __forceinline__ bool head(uint32_t p, uint32_t &q) const {
+        const uint32_t k = idx[p];
+        if (k == start[code(p)]) return false;
+        q = occ[k - 1];
+        return true;
+    }
+    __device__ __forceinline__ uint32_t longest(uint32_t p, uint32_t prev_length, uint32_t &match_start) const {
+        const uint32_t lookahead = n - p;
+        uint32_t chain = dsz::MAX_CHAIN;
+        if (prev_length >= dsz::GOOD_LENGTH) chain >>= 2;
+        const uint32_t nice = dsz::NICE_LENGTH < lookahead ? dsz::NICE_LENGTH : lookahead;
+        const uint32_t cap = uint32_t(dsz::MAX_MATCH) < lookahead ? uint32_t(dsz::MAX_MATCH) : lookahead;
+        const uint32_t limit = p > dsz::MAX_DIST ? p - dsz::MAX_DIST : 0u;
+        const uint32_t k = idx[p];
+        const uint32_t avail = k - start[code(p)];
+        const uint32_t nc = avail < chain ? avail : chain;
+        uint32_t best = prev_length;
+        for (uint32_t base = 0; base < nc; base += 32) {
+            const uint32_t j = base + lane;
+            bool valid = j < nc;
+            const uint32_t q = valid ? occ[k - 1 - j] : 0u;
+            if (j >= 1 && q <= limit) valid = false;          // the chain ends at the first candidate that is too far (or is position 0)
+            uint32_t len = 0;
+            if (valid) {
+                const uint8_t *a = text + q, *b = text + p;
+                while (len < cap && a[len] == b[len]) ++len;
+            }
+            // zlib walks the candidates in order: one replaces the best so far only if strictly longer, and the walk stops at
+            // the first such candidate that reaches nice_length
+            uint32_t incl = len;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, o); if (lane >= uint32_t(o)) incl = incl > t ? incl : t; }
+            uint32_t excl = __shfl_up_sync(0xFFFFFFFFu, incl, 1);
+            if (lane == 0) excl = 0;
+            const uint32_t before = excl > best ? excl : best;
+            const bool improving = valid && len > before;
+            const uint32_t brk = __ballot_sync(0xFFFFFFFFu, improving && len >= nice);
+            const uint32_t upto = brk ? uint32_t(__ffs(int(brk)) - 1) : 31u;
+            const uint32_t cand = (valid && lane <= upto) ? len : 0u;
+            const uint32_t mx = __reduce_max_sync(0xFFFFFFFFu, cand);
+            if (mx > best) {
+                const uint32_t who = uint32_t(__ffs(int(__ballot_sync(0xFFFFFFFFu, cand == mx))) - 1);
+                match_start = __shfl_sync(0xFFFFFFFFu, q, int(who));
+                best = mx;
+            }
+            if (brk) break;
+            if (__ballot_sync(0xFFFFFFFFu, !valid && j < nc)) break;
+        }
+        return best <= lookahead ? best : lookahead;
+    }
+};
+
+// lane 0 owns the trees; every lane learns the stream length after a block
+struct WarpSink {
+    dsz::Trees &T; uint32_t lane;
+    __device__ __forceinline__ void lit(uint8_t c) { if (lane == 0) dsz::tally_lit(T, c); }
+    __device__ __forceinline__ void dist(uint32_t d, uint32_t lc) { if (lane == 0) dsz::tally_dist(T, d, lc); }
+    __device__ __forceinline__ uint64_t flush(uint64_t bits, uint32_t stored_len) {
+        if (lane == 0) bits = dsz::flush_block(T, bits, stored_len, true);
+        __syncwarp();
+        return __shfl_sync(0xFFFFFFFFu, bits, 0);
+    }
+};
+
+constexpr size_t GZ_TREES_BYTES = (sizeof(dsz::Trees) + 15) / 16 * 16;
+constexpr size_t GZ_WARP_SMEM = GZ_TREES_BYTES + (dsz::N_LETTER_CODES + 3) * 4;
+constexpr size_t GZ_SMEM = GZ_WARPS * GZ_WARP_SMEM;
+
+__global__ void __launch_bounds__(GZ_WARPS * 32) gzip_size_kernel(const GzParams P) {
+    extern __shared__ __align__(16) unsigned char gz_smem[];
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    dsz::Trees *const s_trees = reinterpret_cast<dsz::Trees *>(gz_smem + size_t(warp) * GZ_WARP_SMEM);
+    uint32_t *const s_start = reinterpret_cast<uint32_t *>(gz_smem + size_t(warp) * GZ_WARP_SMEM + GZ_TREES_BYTES);
+    const uint64_t slot = uint64_t(blockIdx.x) * GZ_WARPS + warp;
+    const uint32_t cap = uint32_t(P.scratch_stride / 5);
+    uint8_t *const text = P.scratch + slot * P.scratch_stride;
+    uint16_t *const occ = reinterpret_cast<uint16_t *>(text + cap);
+    uint16_t *const idx = occ + cap;
+    uint32_t *const start = s_start;
+    dsz::Trees &T = *s_trees;
+    for (;;) {
+        uint32_t r = 0;
+        if (lane == 0) r = atomicAdd(P.work_counter, 1u);
+        r = __shfl_sync(0xFFFFFFFFu, r, 0);
+        if (r >= P.n_reads) break;
+        const uint32_t seg0 = P.read_seg ? P.read_seg[r] : r, seg1 = P.read_seg ? P.read_seg[r + 1] : r + 1;
+        uint64_t total = 0;
+        for (uint32_t s = seg0; s < seg1; ++s) total += P.seg_len ? P.seg_len[s] : P.seg_off[s + 1] - P.seg_off[s];
+        if (total > dsz::DSZ_MAX_LEN || total > cap) {
+            if (lane == 0) { P.size_out[r] = dsz::DSZ_UNSUPPORTED; if (P.ratio_out) P.ratio_out[r] = __int_as_float(0x7FC00000); }
+            continue;
+        }
+        const uint32_t n = uint32_t(total);
+        // 1. the uppercase dna5 string
+        uint32_t at = 0;
+        for (uint32_t s = seg0; s < seg1; ++s) {
+            const uint64_t off = P.seg_off[s];
+            const uint32_t len = uint32_t(P.seg_len ? P.seg_len[s] : P.seg_off[s + 1] - off);
+            if (P.format == 2) {
+                for (uint32_t i = lane; i < len; i += 32) {
+                    const uint64_t g = off + i;
+                    const uint32_t two = (P.bases[g >> 2] >> ((g & 3u) * 2u)) & 3u;
+                    text[at + i] = uint8_t(0x54474341u >> (two * 8u));      // "ACGT"
+                }
+                if (P.n_exc) {
+                    __syncwarp();
+                    for (uint32_t e = P.exc_seg_off[s] + lane; e < P.exc_seg_off[s + 1]; e += 32) text[at + uint32_t(P.exc_pos[e] - off)] = 'N';
+                }
+            } else {
+                for (uint32_t i = lane; i < len; i += 32) {
+                    const uint32_t rank = base_code(P.bases[off + i]) & 15u;      // dna5 rank A0 C1 G2 N3 T4 (IUPAC -> N, lower case folded, u -> T)
+                    text[at + i] = uint8_t(rank == 0 ? 'A' : (rank == 1 ? 'C' : (rank == 2 ? 'G' : (rank == 4 ? 'T' : 'N'))));
+                }
+            }
+            at += len;
+        }
+        __syncwarp();
+        // 2. stable counting sort of the positions 0 .. n-3 by three-letter code
+        for (uint32_t b = lane; b < uint32_t(dsz::N_LETTER_CODES + 1); b += 32) start[b] = 0;
+        __syncwarp();
+        const uint32_t np = n >= 3 ? n - 2 : 0;
+        WarpMatcher M{text, occ, idx, start, n, lane};
+        for (uint32_t p = lane; p < np; p += 32) atomicAdd(&start[M.code(p) + 1], 1u);
+        __syncwarp();
+        {   // exclusive prefix over 125 counts -> start[b]; start[b + 1] - start[b] = bucket size
+            uint32_t c[4], sum = 0;
+#pragma unroll
+            for (int t = 0; t < 4; ++t) { const uint32_t b = lane * 4 + t; c[t] = b < uint32_t(dsz::N_LETTER_CODES) ? start[b + 1] : 0u; sum += c[t]; }
+            uint32_t incl = sum;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, o); if (lane >= uint32_t(o)) incl += t; }
+            uint32_t run = incl - sum;
+            __syncwarp();
+#pragma unroll
+            for (int t = 0; t < 4; ++t) { const uint32_t b = lane * 4 + t; if (b < uint32_t(dsz::N_LETTER_CODES)) start[b] = run; run += c[t]; }
+            if (lane == 31) start[dsz::N_LETTER_CODES] = incl;
+        }
+        __syncwarp();
+        // fill: chunks of 32 consecutive positions; lanes of one bucket take consecutive slots in lane (= position) order.
+        // idx doubles as the running fill count: cur[b] lives in the upper half of s_start? no — kept in occ's tail is unsafe;
+        // a second 125-entry table is cheap: reuse the Trees area (not in use before the state machine starts)
+        uint32_t *const cur = reinterpret_cast<uint32_t *>(&T);
+        for (uint32_t b = lane; b < uint32_t(dsz::N_LETTER_CODES); b += 32) cur[b] = start[b];
+        __syncwarp();
+        for (uint32_t p0 = 0; p0 < np; p0 += 32) {
+            const uint32_t p = p0 + lane;
+            const bool act = p < np;
+            const uint32_t b = act ? M.code(p) : 0xFFFFu;
+            const uint32_t same = __match_any_sync(0xFFFFFFFFu, b);
+            const uint32_t rank = __popc(same & ((1u << lane) - 1u));
+            const uint32_t leader = uint32_t(__ffs(int(same)) - 1);
+            uint32_t basep = 0;
+            if (act && lane == leader) { basep = cur[b]; cur[b] = basep + uint32_t(__popc(same)); }
+            basep = __shfl_sync(0xFFFFFFFFu, basep, int(leader));
+            if (act) { idx[p] = uint16_t(basep + rank); occ[basep + rank] = uint16_t(p); }
+            __syncwarp();
+        }
+        __syncwarp();
+        // 3 + 4. deflate_slow
+        if (lane == 0) dsz::init_block(T);
+        __syncwarp();
+        WarpSink sink{T, lane};
+        const uint32_t size = dsz::gzip_size(M, sink, n);
+        if (lane == 0) {
+            P.size_out[r] = size;
+            if (P.ratio_out) P.ratio_out[r] = float(double(size) / double(n));
+        }
+        __syncwarp();
+    }
+}
+
+}  // namespace cgk

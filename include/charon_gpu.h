@@ -128,6 +128,7 @@ typedef struct cg_counts_out {
 } cg_counts_out;
 
 /* Per-read host-side scalars feeding the call logic (src/dehost_main.cpp:345-363). */
+/* compression may be NULL: the library then computes it on the device (see cg_compression_batch) */
 typedef struct cg_read_scalars {
     const float *mean_quality;
     const float *compression;
@@ -224,6 +225,20 @@ int cg_classify_batch(cg_handle *h, const cg_batch *batch, const cg_read_scalars
 int cg_eval_batch_static(cg_handle *h, uint32_t n_reads, const uint32_t *num_hashes, const uint32_t *counts,
                          const uint32_t *unique_counts, const cg_read_scalars *scalars, const cg_calls_out *out);
 
+/* ---- per-read compression ratio on the device ------------------------------------------------------------------------
+ * get_compression_ratio (reference src/utils.cpp:114-124, called at src/dehost_main.cpp:359-361 / 449-452): size of
+ * gzip::compress(uppercase dna5 string of the read; both mates of a pair concatenated) = zlib level 6, gzip wrapper, memLevel 8,
+ * divided by the length.  The size is computed bit-exactly without writing the stream (charon_b200/csrc/deflate_size.cuh).
+ * gzip_size_out[n_reads] (may be NULL): bytes; ratio_out[n_reads] (may be NULL): float(double(size) / double(length)) as the
+ * reference forms it.  Reads longer than CG_GZIP_MAX_LEN bases get size 0xFFFFFFFF / ratio NaN (zlib slides its window beyond
+ * that length; compute those on the host).
+ * The same kernel runs inside cg_classify_batch / cg_submit_batch / cg_stage_batch+cg_run_staged when
+ * cg_read_scalars.compression is NULL; there a batch that holds a read longer than CG_GZIP_MAX_LEN is refused (CG_ERR_ARG),
+ * and cg_fetch_compression copies the ratios of the slot's last batch back for the TSV row (after cg_wait_batch). */
+#define CG_GZIP_MAX_LEN 65273u
+int cg_compression_batch(cg_handle *h, const cg_batch *batch, uint32_t *gzip_size_out, float *ratio_out);
+int cg_fetch_compression(cg_handle *h, int slot, float *ratio_out);
+
 /* ---- two-slot pipeline over the same path: cg_submit_batch enqueues H2D + kernels + D2H of one batch on the slot's
  * own stream and returns; cg_wait_batch blocks until that slot's outputs are in the caller's buffers.  With slots 0/1
  * used alternately the PCIe copy of batch i+1 overlaps the kernels of batch i (the chunk loop of
@@ -287,6 +302,7 @@ typedef struct cg_info {
     uint64_t last_h2d_bytes;      /* bytes the last staged batch moved host -> device (bases as sent + offsets + scalars) */
     float last_pack_ms;           /* host wall time of the 4-bit packing (its chunk copies overlap it) */
     uint32_t last_packed;         /* 1 when the last batch went over the link as 4-bit ranks */
+    float last_gzip_kernel_ms;    /* CUDA-event time of the compression-ratio kernel of the last batch (0: ratios came from the host) */
 } cg_info;
 int cg_get_info(cg_handle *h, cg_info *out);
 

@@ -57,7 +57,9 @@ int main() {
     static dsz::Trees T;
     while (std::getline(std::cin, line)) {
         HostMatcher m(reinterpret_cast<const uint8_t *>(line.data()), uint32_t(line.size()));
-        std::printf("%u\n", dsz::gzip_size(m, T, uint32_t(line.size())));
+        dsz::init_block(T);
+        dsz::TreeSink sink{T};
+        std::printf("%u\n", dsz::gzip_size(m, sink, uint32_t(line.size())));
     }
     return 0;
 }

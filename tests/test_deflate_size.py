@@ -62,3 +62,70 @@ def test_restated_deflate_size_equals_zlib_on_the_host(host_exe):
     bad = [(len(s), int(o), gzip_size(s.encode())) for s, o in zip(seqs, out) if int(o) != gzip_size(s.encode())]
     assert not bad, f"{len(bad)} of {len(seqs)} sizes differ from zlib {zlib.ZLIB_RUNTIME_VERSION}; first (length, got, zlib): {bad[:5]}"
     assert gzip_size(b"") == 20 and int(out[0]) == 20
+
+
+def _batch_of(seqs):
+    from tests import common
+    return common.ragged_batch(None, [np.frombuffer(s.encode(), np.uint8) for s in seqs])
+
+
+@pytest.mark.gpu
+def test_gpu_gzip_size_equals_zlib():
+    """cg_compression_batch against the box's zlib: sizes bit-exact, ratios as the reference forms them, both transports."""
+    import charon_b200
+    from tests import common
+    idx, refs = common.build_oracle_index([50_000, 50_000], [0, 1], ["host", "microbial"], seed=41)
+    gpu = common.gpu_from_oracle(idx)
+    try:
+        rng = random.Random(9)
+        seqs = sequences(2, n_random=400) + ["".join(rng.choice("ACGT") for _ in range(n)) for n in LONG]
+        seqs += ["acgtnACGTN" * 300, "ACGURYKM" * 500, "".join(rng.choice("ACGT") for _ in range(65274))]       # folding to dna5; one read past the limit
+        want = np.array([gzip_size(s.upper().translate(str.maketrans("URYKMSWBDHV", "TNNNNNNNNNN")).encode()) for s in seqs], np.uint32)
+        want[-1] = 0xFFFFFFFF
+        bases, seg_off = _batch_of(seqs)
+        for pack in (1, 0):
+            gpu.set_host_pack(pack)
+            got = gpu.compression_batch(bases, seg_off)
+            bad = np.flatnonzero(got["size"] != want)
+            assert bad.size == 0, f"pack {pack}: {bad.size} of {len(seqs)} sizes differ; first: read {bad[0]} length {len(seqs[bad[0]])} gpu {got['size'][bad[0]]} zlib {want[bad[0]]}"
+            lens = np.array([len(s) for s in seqs], np.float64)
+            with np.errstate(divide="ignore", invalid="ignore"):
+                ratio = (want.astype(np.float64) / lens).astype(np.float32)
+            ok = np.arange(len(seqs)) != len(seqs) - 1
+            assert np.array_equal(got["ratio"][ok], ratio[ok]) and np.isnan(got["ratio"][-1])
+        # paired reads: the two mates are compressed as one string (src/dehost_main.cpp:449-452)
+        pairs = seqs[30:90]
+        bases2, seg_off2 = _batch_of(pairs)
+        read_seg = np.arange(0, len(pairs) + 1, 2, dtype=np.uint32)
+        got2 = gpu.compression_batch(bases2, seg_off2, read_seg=read_seg)
+        want2 = np.array([gzip_size((pairs[i] + pairs[i + 1]).encode()) for i in range(0, len(pairs), 2)], np.uint32)
+        assert np.array_equal(got2["size"], want2)
+    finally:
+        gpu.close()
+
+
+@pytest.mark.gpu
+def test_classify_with_ratios_computed_on_the_device():
+    """cg_classify_batch / cg_submit_batch with cg_read_scalars.compression == NULL: same calls as with zlib's ratios passed in."""
+    import charon_b200
+    from tests import common
+    idx, refs = common.build_oracle_index([300_000, 300_000], [0, 1], ["host", "microbial"], seed=43)
+    gpu = common.gpu_from_oracle(idx)
+    try:
+        import oracle
+        gpu.set_model(charon_b200.ClassifyOptions(), host_index=0)                  # min_compression 0.15 (classify_arguments.hpp)
+        n, L = 3000, 3000
+        bases, seg_off, _ = common.fixed_length_batch(8, refs, [0.45, 0.45], n, L)
+        bases[: 40 * L] = np.frombuffer(b"A" * (40 * L), np.uint8)                  # low-complexity reads: the compression gate fires
+        texts = [bytes(bases[i * L:(i + 1) * L]) for i in range(n)]
+        cr = np.array([np.float32(gzip_size(t) / float(L)) for t in texts], np.float32)
+        mq = np.full(n, 20.0, np.float32)
+        ln = np.full(n, L, np.uint32)
+        want = idx.classify_batch(bases, seg_off, mean_q=mq, compression=cr, opts=oracle.default_options(dehost=False))
+        assert (cr < 0.15).sum() == 40 and (want["call"][40:] != 255).any()
+        got = gpu.classify_batch(bases, seg_off, mq, None, ln)
+        common.assert_parity(got, want, prob_rtol=2e-4)
+        assert gpu.info().last_gzip_kernel_ms > 0
+        assert np.array_equal(gpu.fetch_compression(0, n), cr)
+    finally:
+        gpu.close()
