@@ -243,7 +243,8 @@ DS_HD void tally_dist(Trees &T, uint32_t dist, uint32_t lc) {   // dist = match 
 DS_HD uint32_t letter_code(uint8_t c) { return c == 'A' ? 0u : (c == 'C' ? 1u : (c == 'G' ? 2u : (c == 'T' ? 3u : 4u))); }
 
 // The lazy-match state machine of deflate_slow.  M supplies the match search, S receives the symbols:
-//   bool M.head(p, q)                          most recent earlier position with the same three letters (false: none)
+//   bool M.head(p, prev_length, q)             most recent earlier position with the same three letters (false: none);
+//                                              prev_length = the value longest() would get, a hint for what to fetch
 //   uint32_t M.longest(p, prev_length, start)  zlib's longest_match at position p (start: in = previous match start, out = new)
 //   uint8_t M.at(p)                            letter at position p
 //   S.lit(c), S.dist(distance, length - 3)     _tr_tally;  uint64_t S.flush(bits, stored_len)  _tr_flush_block
@@ -259,7 +260,7 @@ DS_HD uint32_t gzip_size(M &m, S &sink, uint32_t n) {
     while (strstart < n) {
         const uint32_t lookahead = n - strstart;
         uint32_t hash_head = 0;
-        const bool has_head = lookahead >= uint32_t(MIN_MATCH) && m.head(strstart, hash_head) && hash_head != 0;
+        const bool has_head = lookahead >= uint32_t(MIN_MATCH) && m.head(strstart, match_length, hash_head) && hash_head != 0;
         prev_length = match_length; prev_match = match_start;
         match_length = MIN_MATCH - 1;
         if (has_head && prev_length < MAX_LAZY && strstart - hash_head <= MAX_DIST) {

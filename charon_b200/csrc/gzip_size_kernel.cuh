@@ -21,45 +21,90 @@ struct GzParams {
     const unsigned long long *exc_pos; const uint32_t *exc_seg_off; unsigned long long n_exc;
     uint32_t n_reads;
     uint32_t *work_counter;
-    uint8_t *scratch; uint64_t scratch_stride;   // per warp: text[cap] | occ u16[cap] | idx u16[cap], cap = scratch_stride / 5
+    uint8_t *scratch; uint64_t scratch_stride; uint32_t cap;   // per warp: text[cap + 64] | idx u32[cap] | occ u16[cap]; scratch_stride = 7 cap + 64
     uint32_t *size_out;                   // gzip size per read (DSZ_UNSUPPORTED: longer than DSZ_MAX_LEN)
     float *ratio_out;                     // float(double(size) / double(length)); may be NULL
 };
 
 constexpr int GZ_WARPS = 8;
 
+// unaligned 8 letters at text + x (text is 8-byte aligned; 16 readable bytes follow every position a compare can reach)
+__device__ __forceinline__ uint64_t load8(const uint8_t *text, uint32_t x) {
+    const uint64_t *w = reinterpret_cast<const uint64_t *>(text + (x & ~7u));
+    const uint64_t lo = w[0], hi = w[1];
+    const uint32_t sh = (x & 7u) * 8u;
+    return sh ? (lo >> sh) | (hi << (64u - sh)) : lo;
+}
+
 struct WarpMatcher {
-    const uint8_t *text; const uint16_t *occ, *idx; const uint32_t *start; uint32_t n, lane;
-    __device__ __forceinline__ uint32_t code(uint32_t p) const {
-        return dsz::letter_code(text[p]) * 25u + dsz::letter_code(text[p + 1]) * 5u + dsz::letter_code(text[p + 2]);
+    const uint8_t *text; const uint16_t *occ; const uint32_t *idx;   // idx[p] = index of p in occ[] | rank of p inside its bucket << 16
+    uint32_t n, np, lane;
+    // register window over the positions [wb, wb + 32): lane i holds idx[wb + i] and text[wb + i]
+    uint32_t wb, iw, tw;
+    // candidates of the position head() was last asked about: lane i holds chain entries i, i + 32, i + 64, i + 96
+    uint32_t cq[4], nc;
+    __device__ __forceinline__ void window(uint32_t p) {   // p never decreases; afterwards wb <= max(p, 1) - 1 and p < wb + 32
+        if (p >= wb + 32u) {
+            wb = p ? p - 1u : 0u;
+            const uint32_t x = wb + lane;
+            iw = x < np ? idx[x] : 0u;
+            tw = x < n ? uint32_t(text[x]) : 0u;
+        }
     }
-    __device__ __forceinline__ uint8_t at(uint32_t p) const { return text[p]; }
-    __device__ __forceinline__ bool head(uint32_t p, uint32_t &q) const {
-        const uint32_t k = idx[p];
-        if (k == start[code(p)]) return false;
-        q = occ[k - 1];
+    __device__ __forceinline__ uint8_t at(uint32_t q) {
+        window(q + 1u);
+        return uint8_t(__shfl_sync(0xFFFFFFFFu, tw, int(q - wb)));
+    }
+    __device__ __forceinline__ bool head(uint32_t p, uint32_t prev_length, uint32_t &q) {
+        window(p);
+        const uint32_t e = __shfl_sync(0xFFFFFFFFu, iw, int(p - wb));
+        const uint32_t k = e & 0xFFFFu, rank = e >> 16;
+        if (rank == 0) return false;
+        const uint32_t chain = prev_length >= dsz::GOOD_LENGTH ? dsz::MAX_CHAIN >> 2 : dsz::MAX_CHAIN;
+        nc = rank < chain ? rank : chain;
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+            const uint32_t j = uint32_t(r) * 32u + lane;
+            cq[r] = j < nc ? uint32_t(occ[k - 1u - j]) : 0u;
+        }
+        q = __shfl_sync(0xFFFFFFFFu, cq[0], 0);
         return true;
     }
-    __device__ __forceinline__ uint32_t longest(uint32_t p, uint32_t prev_length, uint32_t &match_start) const {
+    __device__ __forceinline__ uint32_t longest(uint32_t p, uint32_t prev_length, uint32_t &match_start) {
         const uint32_t lookahead = n - p;
-        uint32_t chain = dsz::MAX_CHAIN;
-        if (prev_length >= dsz::GOOD_LENGTH) chain >>= 2;
         const uint32_t nice = dsz::NICE_LENGTH < lookahead ? dsz::NICE_LENGTH : lookahead;
         const uint32_t cap = uint32_t(dsz::MAX_MATCH) < lookahead ? uint32_t(dsz::MAX_MATCH) : lookahead;
         const uint32_t limit = p > dsz::MAX_DIST ? p - dsz::MAX_DIST : 0u;
-        const uint32_t k = idx[p];
-        const uint32_t avail = k - start[code(p)];
-        const uint32_t nc = avail < chain ? avail : chain;
         uint32_t best = prev_length;
-        for (uint32_t base = 0; base < nc; base += 32) {
-            const uint32_t j = base + lane;
-            bool valid = j < nc;
-            const uint32_t q = valid ? occ[k - 1 - j] : 0u;
-            if (j >= 1 && q <= limit) valid = false;          // the chain ends at the first candidate that is too far (or is position 0)
+        if (best >= cap) return best <= lookahead ? best : lookahead;      // no candidate can be strictly longer
+        // zlib's quick reject, made exact for a whole round: a candidate can only replace the best so far if it is longer than
+        // prev_length, i.e. if it also agrees at offset prev_length.  One letter per candidate decides that for three in four.
+        const uint32_t pb = text[p + best];
+        const uint64_t b0 = load8(text, p);
+        bool valid[4], pass[4];
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+            const uint32_t j = uint32_t(r) * 32u + lane;
+            valid[r] = j < nc && (j == 0 || cq[r] > limit);      // the chain ends at the first candidate that is too far (or is position 0)
+            pass[r] = valid[r] && uint32_t(text[cq[r] + best]) == pb;
+        }
+        uint64_t a0[4];
+#pragma unroll
+        for (int r = 0; r < 4; ++r) a0[r] = pass[r] ? load8(text, cq[r]) : 0ull;
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+            if (uint32_t(r) * 32u >= nc) break;
+            const uint32_t j = uint32_t(r) * 32u + lane, q = cq[r];
             uint32_t len = 0;
-            if (valid) {
-                const uint8_t *a = text + q, *b = text + p;
-                while (len < cap && a[len] == b[len]) ++len;
+            if (pass[r]) {
+                uint64_t x = a0[r] ^ b0;
+                while (x == 0) {
+                    len += 8;
+                    if (len >= cap) break;
+                    x = load8(text, q + len) ^ load8(text, p + len);
+                }
+                if (x) len += uint32_t(__ffsll((long long)x) - 1) >> 3;
+                len = len < cap ? len : cap;
             }
             // zlib walks the candidates in order: one replaces the best so far only if strictly longer, and the walk stops at
             // the first such candidate that reaches nice_length
@@ -69,10 +114,10 @@ struct WarpMatcher {
             uint32_t excl = __shfl_up_sync(0xFFFFFFFFu, incl, 1);
             if (lane == 0) excl = 0;
             const uint32_t before = excl > best ? excl : best;
-            const bool improving = valid && len > before;
+            const bool improving = valid[r] && len > before;
             const uint32_t brk = __ballot_sync(0xFFFFFFFFu, improving && len >= nice);
             const uint32_t upto = brk ? uint32_t(__ffs(int(brk)) - 1) : 31u;
-            const uint32_t cand = (valid && lane <= upto) ? len : 0u;
+            const uint32_t cand = (valid[r] && lane <= upto) ? len : 0u;
             const uint32_t mx = __reduce_max_sync(0xFFFFFFFFu, cand);
             if (mx > best) {
                 const uint32_t who = uint32_t(__ffs(int(__ballot_sync(0xFFFFFFFFu, cand == mx))) - 1);
@@ -80,7 +125,7 @@ struct WarpMatcher {
                 best = mx;
             }
             if (brk) break;
-            if (__ballot_sync(0xFFFFFFFFu, !valid && j < nc)) break;
+            if (__ballot_sync(0xFFFFFFFFu, !valid[r] && j < nc)) break;
         }
         return best <= lookahead ? best : lookahead;
     }
@@ -108,10 +153,10 @@ __global__ void __launch_bounds__(GZ_WARPS * 32) gzip_size_kernel(const GzParams
     dsz::Trees *const s_trees = reinterpret_cast<dsz::Trees *>(gz_smem + size_t(warp) * GZ_WARP_SMEM);
     uint32_t *const s_start = reinterpret_cast<uint32_t *>(gz_smem + size_t(warp) * GZ_WARP_SMEM + GZ_TREES_BYTES);
     const uint64_t slot = uint64_t(blockIdx.x) * GZ_WARPS + warp;
-    const uint32_t cap = uint32_t(P.scratch_stride / 5);
+    const uint32_t cap = P.cap;
     uint8_t *const text = P.scratch + slot * P.scratch_stride;
-    uint16_t *const occ = reinterpret_cast<uint16_t *>(text + cap);
-    uint16_t *const idx = occ + cap;
+    uint32_t *const idx = reinterpret_cast<uint32_t *>(text + cap + 64);
+    uint16_t *const occ = reinterpret_cast<uint16_t *>(idx + cap);
     uint32_t *const start = s_start;
     dsz::Trees &T = *s_trees;
     for (;;) {
@@ -150,13 +195,15 @@ __global__ void __launch_bounds__(GZ_WARPS * 32) gzip_size_kernel(const GzParams
             }
             at += len;
         }
+        if (lane < 8) reinterpret_cast<uint32_t *>(text + ((n + 3u) & ~3u))[lane] = 0u;   // 32 zero bytes behind the text (the scratch still holds the previous read)
+        if (lane < 4 && n + lane < ((n + 3u) & ~3u)) text[n + lane] = 0;
         __syncwarp();
         // 2. stable counting sort of the positions 0 .. n-3 by three-letter code
         for (uint32_t b = lane; b < uint32_t(dsz::N_LETTER_CODES + 1); b += 32) start[b] = 0;
         __syncwarp();
         const uint32_t np = n >= 3 ? n - 2 : 0;
-        WarpMatcher M{text, occ, idx, start, n, lane};
-        for (uint32_t p = lane; p < np; p += 32) atomicAdd(&start[M.code(p) + 1], 1u);
+        auto code3 = [&](uint32_t p) -> uint32_t { return dsz::letter_code(text[p]) * 25u + dsz::letter_code(text[p + 1]) * 5u + dsz::letter_code(text[p + 2]); };
+        for (uint32_t p = lane; p < np; p += 32) atomicAdd(&start[code3(p) + 1], 1u);
         __syncwarp();
         {   // exclusive prefix over 125 counts -> start[b]; start[b + 1] - start[b] = bucket size
             uint32_t c[4], sum = 0;
@@ -181,14 +228,14 @@ __global__ void __launch_bounds__(GZ_WARPS * 32) gzip_size_kernel(const GzParams
         for (uint32_t p0 = 0; p0 < np; p0 += 32) {
             const uint32_t p = p0 + lane;
             const bool act = p < np;
-            const uint32_t b = act ? M.code(p) : 0xFFFFu;
+            const uint32_t b = act ? code3(p) : 0xFFFFu;
             const uint32_t same = __match_any_sync(0xFFFFFFFFu, b);
             const uint32_t rank = __popc(same & ((1u << lane) - 1u));
             const uint32_t leader = uint32_t(__ffs(int(same)) - 1);
             uint32_t basep = 0;
             if (act && lane == leader) { basep = cur[b]; cur[b] = basep + uint32_t(__popc(same)); }
             basep = __shfl_sync(0xFFFFFFFFu, basep, int(leader));
-            if (act) { idx[p] = uint16_t(basep + rank); occ[basep + rank] = uint16_t(p); }
+            if (act) { const uint32_t k = basep + rank; idx[p] = k | ((k - start[b]) << 16); occ[k] = uint16_t(p); }
             __syncwarp();
         }
         __syncwarp();
@@ -196,6 +243,8 @@ __global__ void __launch_bounds__(GZ_WARPS * 32) gzip_size_kernel(const GzParams
         if (lane == 0) dsz::init_block(T);
         __syncwarp();
         WarpSink sink{T, lane};
+        WarpMatcher M{text, occ, idx, n, np, lane, 0xFFFFFF00u, 0u, 0u, {0u, 0u, 0u, 0u}, 0u};
+        M.wb = 0u - 32u;      // nothing windowed yet: wb + 32 == 0, the first window() call loads
         const uint32_t size = dsz::gzip_size(M, sink, n);
         if (lane == 0) {
             P.size_out[r] = size;

@@ -63,6 +63,7 @@ struct Batch {
     std::vector<ReadRow> rows;
     std::vector<std::vector<uint64_t>> read_exc;   // per read: batch positions of its non-ACGT bases (almost always empty)
     uint64_t seq = 0;
+    bool device_cr = false;                        // the compression ratios of this batch are computed on the GPU (--gpu_compression)
     bool paired_mismatch = false;                  // reader: the pair after the last row of this batch has differing ids
     std::string mismatch_text;
 };
@@ -199,7 +200,7 @@ private:
     void run_pipeline();
     void reader_thread(BoundedQueue<Batch> &parsed);
     void writer_thread(BoundedQueue<std::vector<ReadRow>> &done);
-    void prepare_batch(Batch &b, int slot);
+    void prepare_batch(Batch &b, int slot, bool allow_device_cr);
     void submit_batch(Batch &b, int slot, bool with_eval);
     void collect_batch(Batch &b, int slot, bool with_eval);
     void train_batch(Batch &b, std::vector<ReadRow> &to_print);

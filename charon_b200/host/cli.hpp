@@ -57,6 +57,7 @@ inline std::string usage(bool dehost) {
     s += "  -t,--threads INT              Maximum number of threads to use.\n";
     s += "  -v                            Verbosity of logging. Repeat for increased verbosity\n";
     s += "  --gpus INT                    [charon-b200] number of B200 GPUs to shard read batches over (default 1).\n";
+    s += "  --gpu_compression             [charon-b200] compute the gzip compression ratio of every read on the GPU (bit-exact zlib level-6 size) instead of with zlib on the -t threads.\n";
     s += "  --partition_filter            [charon-b200] split the filter by row range over the GPUs (NVLink peer reads) instead of replicating it.\n";
     s += "  --batch_reads INT             [charon-b200] reads per GPU batch (default 16384).\n";
     return s;
@@ -115,6 +116,7 @@ inline bool parse_subcommand(bool dehost, int argc, char **argv, int first, Opti
         else if (a == "-t" || a == "--threads") o.threads = uint8_t(detail::to_int(a, need(), 0, 255));
         else if (a == "--gpus") o.gpus = int(detail::to_int(a, need(), 1, 64));
         else if (a == "--partition_filter") o.partition_filter = true;
+        else if (a == "--gpu_compression") o.gpu_compression = true;
         else if (a == "--batch_reads") o.batch_reads = uint32_t(detail::to_int(a, need(), 1, 1 << 22));
         else if (a.size() >= 2 && a[0] == '-' && a.find_first_not_of('v', 1) == std::string::npos) o.verbosity = uint8_t(o.verbosity + a.size() - 1);
         else if (!a.empty() && a[0] == '-' && a.size() > 1) throw CliError("The following argument was not expected: " + a);

@@ -48,6 +48,7 @@ struct Options {
     // B200 extensions (not in the reference CLI)
     int gpus = 1;
     uint32_t batch_reads = 16384;
+    bool gpu_compression = false;    // compute the gzip compression ratio of the reads on the GPU (cg_read_scalars.compression = NULL)
     bool partition_filter = false;   // split the filter by row range over --gpus GPUs instead of replicating it
 
     static Options dehost_defaults() { return Options(); }

@@ -23,7 +23,7 @@ struct HostMatcher {
     }
     uint32_t code(uint32_t p) const { return dsz::letter_code(text[p]) * 25 + dsz::letter_code(text[p + 1]) * 5 + dsz::letter_code(text[p + 2]); }
     uint8_t at(uint32_t p) const { return text[p]; }
-    bool head(uint32_t p, uint32_t &q) const {
+    bool head(uint32_t p, uint32_t, uint32_t &q) const {
         const uint32_t b = code(p);
         if (idx[p] == start[b]) return false;
         q = occ[idx[p] - 1];

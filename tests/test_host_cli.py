@@ -251,6 +251,51 @@ def test_dehost_extract_trains_then_classifies(charon, small_index, tmp_path):
 
 
 @pytest.mark.gpu
+def test_gpu_compression_flag_gives_the_same_bytes(charon, small_index, tmp_path):
+    """--gpu_compression: the compression ratio column and every call that depends on it come from gzip_size_kernel (zlib
+    level-6 gzip size, bit-exact) instead of zlib on the host threads: stdout must not change — single reads (with a tiny, an
+    empty, a low-complexity and an over-long read, whose batch falls back to the host), paired reads, and --extract."""
+    idx, refs, idx_path = small_index
+    reads = _mixed_reads(refs, 300, seed=15)
+    reads.insert(3, ("tiny", "ACGTACG", "IIIIIII"))
+    reads.insert(9, ("empty", "", ""))
+    reads.insert(20, ("polyA", "A" * 2000, "I" * 2000))
+    rng = np.random.default_rng(3)
+    big = "".join(rng.choice(list("ACGT"), 70_000))
+    reads.insert(150, ("too_long_for_the_kernel", big, "I" * len(big)))
+    fq = str(tmp_path / "r.fq")
+    _write_fastq(fq, reads)
+    want = _oracle_tsv(idx, [(r,) for r in reads], oracle.default_options(True))
+    for flag in ([], ["--gpu_compression"]):
+        got = run(charon, "dehost", fq, "--db", idx_path, "-t", "2", "--batch_reads", "50", *flag, cwd=tmp_path)
+        assert got.returncode == 0, got.stderr
+        assert got.stdout == want, flag
+    # paired
+    a = _mixed_reads(refs, 90, seed=17, min_len=60, max_len=300)
+    b = _mixed_reads(refs, 90, seed=18, min_len=60, max_len=300)
+    r1 = [(f"pair{i}/1", s, q) for i, (_, s, q) in enumerate(a)]
+    r2 = [(f"pair{i}/2", s, q) for i, (_, s, q) in enumerate(b)]
+    f1, f2 = str(tmp_path / "p_1.fq"), str(tmp_path / "p_2.fq")
+    _write_fastq(f1, r1); _write_fastq(f2, r2)
+    o = oracle.default_options(True)
+    o.dehost = 0
+    o.min_length = 80
+    got = run(charon, "dehost", f1, f2, "--db", idx_path, "--gpu_compression", "--batch_reads", "40", cwd=tmp_path)
+    assert got.returncode == 0, got.stderr
+    assert got.stdout == _oracle_tsv(idx, list(zip(r1, r2)), o)
+    # --extract: training batches keep the host's ratios, the rest use the kernel's
+    reads = _mixed_reads(refs, 500, seed=19, min_len=400, max_len=3000)
+    fq = str(tmp_path / "e.fastq")
+    _write_fastq(fq, reads)
+    o = oracle.default_options(True)
+    o.run_extract = 1
+    o.num_reads_to_fit = 25
+    got = run(charon, "dehost", fq, "--db", idx_path, "-e", "microbial", "-p", "outg", "--num_reads_to_fit", "25", "--batch_reads", "64", "--gpu_compression", cwd=tmp_path)
+    assert got.returncode == 0, got.stderr
+    assert got.stdout == _oracle_tsv(idx, [(r,) for r in reads], o)
+
+
+@pytest.mark.gpu
 def test_classify_three_categories(charon, tmp_path):
     idx, refs = common.build_oracle_index([200_000, 150_000, 120_000, 90_000], [0, 1, 1, 2], ["bacteria", "host", "virus"], seed=31)
     p = str(tmp_path / "three.idx")
