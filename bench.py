@@ -467,6 +467,28 @@ def run_b200(args, name, wl):
     serial_ms, _, _, _ = gpu.timer_stop()
     barrier()
     serial_ms = max_over_ranks(serial_ms)
+    # ---- the compression-ratio scalar of the same batch on the device (outside the timed regions above: the
+    #      bench's scalars are given, as BASELINE's metric has them), checked against the box's zlib on a sample -----------------
+    gz_sizes = pinned_array((R,), np.uint32)
+    gz_ratio = pinned_array((R,), np.float32)
+    gz_ms = []
+    for _ in range(2):
+        gpu._check(Lb.cg_compression_batch(gpu._h, C.byref(batch_2bit), gz_sizes.ctypes.data, gz_ratio.ctypes.data), "cg_compression_batch")
+        gz_ms.append(float(gpu.info().last_gzip_kernel_ms))
+    import zlib
+    n_gz = min(R, 300)
+    t_z = time.time()
+    z_sizes = []
+    for i in range(n_gz):
+        zc = zlib.compressobj(-1, zlib.DEFLATED, 31, 8, 0)
+        z_sizes.append(len(zc.compress(bytes(bases[i * L:(i + 1) * L]).upper()) + zc.flush()))
+    t_z = time.time() - t_z
+    compression = {"what": "gzip size (zlib level 6, gzip wrapper, memLevel 8: reference src/utils.cpp:114-124) of every read of the step, cg_compression_batch",
+                   "gzip_kernel_ms": min(gz_ms), "reads_per_sec": R / (min(gz_ms) / 1e3), "sizes_equal_zlib_on_sample": bool(np.array_equal(gz_sizes[:n_gz], np.array(z_sizes, np.uint32))),
+                   "sample_reads": n_gz, "zlib_version": zlib.ZLIB_RUNTIME_VERSION, "zlib_one_core_reads_per_sec": n_gz / t_z, "mean_ratio": float(np.mean(gz_ratio))}
+    if not compression["sizes_equal_zlib_on_sample"]:
+        sys.stderr.write("bench.py: PARITY FAILURE: gzip sizes from the device differ from zlib\n")
+        os._exit(3)
     # ---- what the memory system gives a kernel that ONLY gathers, on this very filter -------------------------
     g_query_ms = gpu.bench_gather(minimisers, mode=0, reps=5)
     g_sector_ms = gpu.bench_gather(3 * minimisers, mode=1, reps=5)
@@ -499,7 +521,7 @@ def run_b200(args, name, wl):
     line = {"metric": "reads_per_sec", "value": value, "unit": "reads/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ra["total_ms"] / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64",
             "data": "synthetic", "config": shared_config(name, wl),
-            "details": {"filter_partitioned": partitioned, "partition_check": part_check, "reads_per_step_per_gpu": R,
+            "details": {"compression_on_device": compression, "filter_partitioned": partitioned, "partition_check": part_check, "reads_per_step_per_gpu": R,
                         "filter_rows": int(info.bin_size), "filter_bytes_hbm": int(info.filter_bytes), "row_bits": int(info.row_bits),
                         "minimisers_per_step_per_gpu": minimisers, "classified_frac": float((res["call"] != 255).mean()),
                         "hbm_resident_bases": "2 bits per base (CG_BASES_2BIT), every read on a 64-base boundary",

@@ -557,6 +557,7 @@ int launch_gzip(cg_handle *h, float *ratio_out) {
     G.n_reads = n; G.work_counter = h->counter.as<uint32_t>();
     G.scratch = h->gz_scratch.as<uint8_t>(); G.scratch_stride = cap * 7 + 64; G.cap = uint32_t(cap);
     G.size_out = h->gz_size.as<uint32_t>(); G.ratio_out = ratio_out;
+    { const char *e = std::getenv("CHARON_GZ_PREFETCH"); G.prefetch = e ? uint32_t(std::atoi(e)) : 0u; }   // measured: no gain (the step is a chain of dependent instructions, not a wait for memory)
     CU(h, cudaMemsetAsync(h->counter.p, 0, 4, h->stream));
     cgk::gzip_size_kernel<<<grid, cgk::GZ_WARPS * 32, cgk::GZ_SMEM, h->stream>>>(G);
     CU(h, cudaGetLastError());

@@ -30,6 +30,14 @@
 
 namespace dsz {
 
+DS_HD int msb32(uint32_t x) {     // index of the highest set bit, x != 0
+#ifdef __CUDA_ARCH__
+    return 31 - __clz(int(x));
+#else
+    return 31 - __builtin_clz(x);
+#endif
+}
+
 constexpr int L_CODES = 286, D_CODES = 30, BL_CODES = 19, HEAP_SIZE = 2 * L_CODES + 1, MAX_BITS = 15, MAX_BL_BITS = 7;
 constexpr int END_BLOCK = 256, REP_3_6 = 16, REPZ_3_10 = 17, REPZ_11_138 = 18;
 constexpr int MIN_MATCH = 3, MAX_MATCH = 258, MIN_LOOKAHEAD = MAX_MATCH + MIN_MATCH + 1, W_SIZE = 32768;
@@ -44,18 +52,14 @@ constexpr int N_LETTER_CODES = 125;                      // 5^3 three-letter str
 DS_HD int length_code(uint32_t lc) {
     if (lc < 8) return int(lc);
     if (lc == 255) return 28;
-    int msb = 31;
-    while (!(lc >> msb)) --msb;
-    const int e = msb - 2;
+    const int e = msb32(lc) - 2;
     return 4 * (e + 1) + int((lc - (4u << e)) >> e);
 }
 DS_HD int extra_lbits(int code) { return (code < 8 || code == 28) ? 0 : (code >> 2) - 1; }
 // distance - 1 in [0, 32767] -> distance code 0..29, and its extra bits
 DS_HD int dist_code(uint32_t d) {
     if (d < 4) return int(d);
-    int msb = 31;
-    while (!(d >> msb)) --msb;
-    const int e = msb - 1;
+    const int e = msb32(d) - 1;
     return 2 * (e + 1) + int((d >> e) & 1u);
 }
 DS_HD int extra_dbits(int code) { return code < 4 ? 0 : (code >> 1) - 1; }
@@ -73,7 +77,7 @@ DS_HD int bl_order(int i) {
 // are separate arrays, which changes nothing as long as the read/write order of gen_bitlen is kept.
 struct Trees {
     uint16_t lfreq[HEAP_SIZE], dfreq[2 * D_CODES + 1], blfreq[2 * BL_CODES + 1];
-    uint16_t llen[HEAP_SIZE + 1], dlen[2 * D_CODES + 2], bllen[2 * BL_CODES + 1];   // +1: the guard scan_tree writes at max_code + 1
+    uint8_t llen[HEAP_SIZE + 1], dlen[2 * D_CODES + 2], bllen[2 * BL_CODES + 1];    // +1: the guard scan_tree writes at max_code + 1 (0xff here, 0xffff in zlib: no length is either)
     uint16_t dad[HEAP_SIZE];
     uint16_t heap[HEAP_SIZE];
     uint8_t depth[HEAP_SIZE];
@@ -112,7 +116,7 @@ DS_HD void pqdownheap(Trees &T, const uint16_t *freq, int k) {
 template <int WHICH>
 DS_HD int build_tree(Trees &T) {
     uint16_t *freq = WHICH == 0 ? T.lfreq : (WHICH == 1 ? T.dfreq : T.blfreq);
-    uint16_t *len = WHICH == 0 ? T.llen : (WHICH == 1 ? T.dlen : T.bllen);
+    uint8_t *len = WHICH == 0 ? T.llen : (WHICH == 1 ? T.dlen : T.bllen);
     constexpr int elems = WHICH == 0 ? L_CODES : (WHICH == 1 ? D_CODES : BL_CODES);
     constexpr int max_length = WHICH == 2 ? MAX_BL_BITS : MAX_BITS;
     constexpr int base = WHICH == 0 ? 257 : 0;
@@ -153,7 +157,7 @@ DS_HD int build_tree(Trees &T) {
         const int n = T.heap[h];
         int bits = len[T.dad[n]] + 1;
         if (bits > max_length) { bits = max_length; overflow++; }
-        len[n] = uint16_t(bits);
+        len[n] = uint8_t(bits);
         if (n > max_code) continue;
         T.bl_count[bits]++;
         const int xb = xbits_of(n);
@@ -177,7 +181,7 @@ DS_HD int build_tree(Trees &T) {
                 if (m > max_code) continue;
                 if (len[m] != unsigned(bits)) {
                     T.opt_len += (uint32_t(bits) - uint32_t(len[m])) * uint32_t(freq[m]);
-                    len[m] = uint16_t(bits);
+                    len[m] = uint8_t(bits);
                 }
                 n--;
             }
@@ -186,10 +190,10 @@ DS_HD int build_tree(Trees &T) {
     return max_code;
 }
 
-DS_HD void scan_tree(Trees &T, uint16_t *len, int max_code) {
+DS_HD void scan_tree(Trees &T, uint8_t *len, int max_code) {
     int prevlen = -1, nextlen = len[0], count = 0, max_count = 7, min_count = 4;
     if (nextlen == 0) { max_count = 138; min_count = 3; }
-    len[max_code + 1] = 0xFFFF;
+    len[max_code + 1] = 0xFF;
     for (int n = 0; n <= max_code; ++n) {
         const int curlen = nextlen;
         nextlen = len[n + 1];

@@ -22,51 +22,72 @@ struct GzParams {
     uint32_t n_reads;
     uint32_t *work_counter;
     uint8_t *scratch; uint64_t scratch_stride; uint32_t cap;   // per warp: text[cap + 64] | idx u32[cap] | occ u16[cap]; scratch_stride = 7 cap + 64
+    uint32_t prefetch;                    // fetch the predicted next position's chain candidates one step early
     uint32_t *size_out;                   // gzip size per read (DSZ_UNSUPPORTED: longer than DSZ_MAX_LEN)
     float *ratio_out;                     // float(double(size) / double(length)); may be NULL
 };
 
 constexpr int GZ_WARPS = 8;
 
-// unaligned 8 letters at text + x (text is 8-byte aligned; 16 readable bytes follow every position a compare can reach)
+// unaligned 8 letters at text + x (text is 4-byte aligned; 12 readable bytes follow every position a compare can reach)
 __device__ __forceinline__ uint64_t load8(const uint8_t *text, uint32_t x) {
-    const uint64_t *w = reinterpret_cast<const uint64_t *>(text + (x & ~7u));
-    const uint64_t lo = w[0], hi = w[1];
-    const uint32_t sh = (x & 7u) * 8u;
-    return sh ? (lo >> sh) | (hi << (64u - sh)) : lo;
+    const uint32_t *w = reinterpret_cast<const uint32_t *>(text + (x & ~3u));
+    const uint32_t w0 = w[0], w1 = w[1], w2 = w[2], sh = (x & 3u) * 8u;
+    return uint64_t(__funnelshift_r(w0, w1, sh)) | (uint64_t(__funnelshift_r(w1, w2, sh)) << 32);
 }
 
 struct WarpMatcher {
-    const uint8_t *text; const uint16_t *occ; const uint32_t *idx;   // idx[p] = index of p in occ[] | rank of p inside its bucket << 16
+    const uint8_t *text;             // shared memory when the read fits there, else the warp's global scratch
+    const uint16_t *occ; const uint32_t *idx;   // idx[p] = index of p in occ[] | rank of p inside its bucket << 16
     uint32_t n, np, lane;
-    // register window over the positions [wb, wb + 32): lane i holds idx[wb + i] and text[wb + i]
-    uint32_t wb, iw, tw;
-    // candidates of the position head() was last asked about: lane i holds chain entries i, i + 32, i + 64, i + 96
+    // register window over idx[wb .. wb + 64): lane i holds idx[wb + i] and idx[wb + 32 + i]; the upper half is fetched one
+    // half ahead of its use
+    uint32_t wb, iwA, iwB;
+    // chain candidates (lane i: entries i, i + 32, i + 64, i + 96 of the chain) of the position being searched, and of the
+    // position predicted to be searched next (fetched one step early: their latency hides behind this step)
     uint32_t cq[4], nc;
-    __device__ __forceinline__ void window(uint32_t p) {   // p never decreases; afterwards wb <= max(p, 1) - 1 and p < wb + 32
-        if (p >= wb + 32u) {
-            wb = p ? p - 1u : 0u;
-            const uint32_t x = wb + lane;
-            iw = x < np ? idx[x] : 0u;
-            tw = x < n ? uint32_t(text[x]) : 0u;
-        }
+    uint32_t pq[4], prank, ppos;
+    bool prefetch;
+    __device__ __forceinline__ uint32_t ld_idx(uint32_t x) const { return x < np ? idx[x] : 0u; }
+    __device__ __forceinline__ void advance(uint32_t p) {      // p never decreases
+        if (p - wb >= 64u) { wb = p; iwA = ld_idx(wb + lane); iwB = ld_idx(wb + 32u + lane); }
+        else if (p - wb >= 32u) { iwA = iwB; wb += 32u; iwB = ld_idx(wb + 32u + lane); }
     }
-    __device__ __forceinline__ uint8_t at(uint32_t q) {
-        window(q + 1u);
-        return uint8_t(__shfl_sync(0xFFFFFFFFu, tw, int(q - wb)));
+    __device__ __forceinline__ uint32_t entry(uint32_t x) const {   // wb <= x < wb + 64
+        const uint32_t d = x - wb;
+        const uint32_t a = __shfl_sync(0xFFFFFFFFu, iwA, int(d & 31u)), b = __shfl_sync(0xFFFFFFFFu, iwB, int(d & 31u));
+        return d < 32u ? a : b;
     }
-    __device__ __forceinline__ bool head(uint32_t p, uint32_t prev_length, uint32_t &q) {
-        window(p);
-        const uint32_t e = __shfl_sync(0xFFFFFFFFu, iw, int(p - wb));
-        const uint32_t k = e & 0xFFFFu, rank = e >> 16;
-        if (rank == 0) return false;
-        const uint32_t chain = prev_length >= dsz::GOOD_LENGTH ? dsz::MAX_CHAIN >> 2 : dsz::MAX_CHAIN;
-        nc = rank < chain ? rank : chain;
+    __device__ __forceinline__ void fetch(uint32_t e, uint32_t (&q)[4], uint32_t &rank) const {   // up to MAX_CHAIN candidates
+        const uint32_t k = e & 0xFFFFu;
+        rank = e >> 16;
+        const uint32_t m = rank < dsz::MAX_CHAIN ? rank : dsz::MAX_CHAIN;
 #pragma unroll
         for (int r = 0; r < 4; ++r) {
             const uint32_t j = uint32_t(r) * 32u + lane;
-            cq[r] = j < nc ? uint32_t(occ[k - 1u - j]) : 0u;
+            q[r] = 0u;
+            if (uint32_t(r) * 32u < m && j < m) q[r] = uint32_t(occ[k - 1u - j]);
         }
+    }
+    __device__ __forceinline__ uint8_t at(uint32_t q) const { return text[q]; }
+    __device__ __forceinline__ bool head(uint32_t p, uint32_t prev_length, uint32_t &q) {
+        advance(p);
+        uint32_t rank;
+        if (ppos == p) {
+#pragma unroll
+            for (int r = 0; r < 4; ++r) cq[r] = pq[r];
+            rank = prank;
+        } else {
+            fetch(entry(p), cq, rank);
+        }
+        const uint32_t chain = prev_length >= dsz::GOOD_LENGTH ? dsz::MAX_CHAIN >> 2 : dsz::MAX_CHAIN;
+        nc = rank < chain ? rank : chain;
+        // the position searched next: with a match of prev_length pending at p - 1, p + prev_length - 1 unless this position
+        // finds a longer one (lazy evaluation); without one, always p + 1
+        const uint32_t t = prev_length >= uint32_t(dsz::MIN_MATCH) ? p + prev_length - 1u : p + 1u;
+        ppos = 0xFFFFFFFFu;
+        if (prefetch && t < np && t - wb < 64u) { fetch(entry(t), pq, prank); ppos = t; }
+        if (rank == 0) return false;
         q = __shfl_sync(0xFFFFFFFFu, cq[0], 0);
         return true;
     }
@@ -84,13 +105,16 @@ struct WarpMatcher {
         bool valid[4], pass[4];
 #pragma unroll
         for (int r = 0; r < 4; ++r) {
-            const uint32_t j = uint32_t(r) * 32u + lane;
-            valid[r] = j < nc && (j == 0 || cq[r] > limit);      // the chain ends at the first candidate that is too far (or is position 0)
-            pass[r] = valid[r] && uint32_t(text[cq[r] + best]) == pb;
+            valid[r] = false; pass[r] = false;
+            if (uint32_t(r) * 32u < nc) {                        // warp-uniform: most chains need one or two rounds
+                const uint32_t j = uint32_t(r) * 32u + lane;
+                valid[r] = j < nc && (j == 0 || cq[r] > limit);  // the chain ends at the first candidate that is too far (or is position 0)
+                pass[r] = valid[r] && uint32_t(text[cq[r] + best]) == pb;
+            }
         }
         uint64_t a0[4];
 #pragma unroll
-        for (int r = 0; r < 4; ++r) a0[r] = pass[r] ? load8(text, cq[r]) : 0ull;
+        for (int r = 0; r < 4; ++r) { a0[r] = 0ull; if (uint32_t(r) * 32u < nc && pass[r]) a0[r] = load8(text, cq[r]); }
 #pragma unroll
         for (int r = 0; r < 4; ++r) {
             if (uint32_t(r) * 32u >= nc) break;
@@ -108,23 +132,26 @@ struct WarpMatcher {
             }
             // zlib walks the candidates in order: one replaces the best so far only if strictly longer, and the walk stops at
             // the first such candidate that reaches nice_length
-            uint32_t incl = len;
+            const uint32_t any = __ballot_sync(0xFFFFFFFFu, len > best);
+            if (any) {
+                uint32_t incl = len;
 #pragma unroll
-            for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, o); if (lane >= uint32_t(o)) incl = incl > t ? incl : t; }
-            uint32_t excl = __shfl_up_sync(0xFFFFFFFFu, incl, 1);
-            if (lane == 0) excl = 0;
-            const uint32_t before = excl > best ? excl : best;
-            const bool improving = valid[r] && len > before;
-            const uint32_t brk = __ballot_sync(0xFFFFFFFFu, improving && len >= nice);
-            const uint32_t upto = brk ? uint32_t(__ffs(int(brk)) - 1) : 31u;
-            const uint32_t cand = (valid[r] && lane <= upto) ? len : 0u;
-            const uint32_t mx = __reduce_max_sync(0xFFFFFFFFu, cand);
-            if (mx > best) {
-                const uint32_t who = uint32_t(__ffs(int(__ballot_sync(0xFFFFFFFFu, cand == mx))) - 1);
-                match_start = __shfl_sync(0xFFFFFFFFu, q, int(who));
-                best = mx;
+                for (int o = 1; o < 32; o <<= 1) { const uint32_t t = __shfl_up_sync(0xFFFFFFFFu, incl, o); if (lane >= uint32_t(o)) incl = incl > t ? incl : t; }
+                uint32_t excl = __shfl_up_sync(0xFFFFFFFFu, incl, 1);
+                if (lane == 0) excl = 0;
+                const uint32_t before = excl > best ? excl : best;
+                const bool improving = valid[r] && len > before;
+                const uint32_t brk = __ballot_sync(0xFFFFFFFFu, improving && len >= nice);
+                const uint32_t upto = brk ? uint32_t(__ffs(int(brk)) - 1) : 31u;
+                const uint32_t cand = (valid[r] && lane <= upto) ? len : 0u;
+                const uint32_t mx = __reduce_max_sync(0xFFFFFFFFu, cand);
+                if (mx > best) {
+                    const uint32_t who = uint32_t(__ffs(int(__ballot_sync(0xFFFFFFFFu, cand == mx))) - 1);
+                    match_start = __shfl_sync(0xFFFFFFFFu, q, int(who));
+                    best = mx;
+                }
+                if (brk) break;
             }
-            if (brk) break;
             if (__ballot_sync(0xFFFFFFFFu, !valid[r] && j < nc)) break;
         }
         return best <= lookahead ? best : lookahead;
@@ -144,7 +171,8 @@ struct WarpSink {
 };
 
 constexpr size_t GZ_TREES_BYTES = (sizeof(dsz::Trees) + 15) / 16 * 16;
-constexpr size_t GZ_WARP_SMEM = GZ_TREES_BYTES + (dsz::N_LETTER_CODES + 3) * 4;
+constexpr uint32_t GZ_SMEM_TEXT = 8192 + 64;     // reads of up to 8192 letters keep their text in shared memory
+constexpr size_t GZ_WARP_SMEM = GZ_TREES_BYTES + (dsz::N_LETTER_CODES + 3) * 4 + GZ_SMEM_TEXT;
 constexpr size_t GZ_SMEM = GZ_WARPS * GZ_WARP_SMEM;
 
 __global__ void __launch_bounds__(GZ_WARPS * 32) gzip_size_kernel(const GzParams P) {
@@ -152,10 +180,11 @@ __global__ void __launch_bounds__(GZ_WARPS * 32) gzip_size_kernel(const GzParams
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     dsz::Trees *const s_trees = reinterpret_cast<dsz::Trees *>(gz_smem + size_t(warp) * GZ_WARP_SMEM);
     uint32_t *const s_start = reinterpret_cast<uint32_t *>(gz_smem + size_t(warp) * GZ_WARP_SMEM + GZ_TREES_BYTES);
+    uint8_t *const text_s = reinterpret_cast<uint8_t *>(s_start + dsz::N_LETTER_CODES + 3);
     const uint64_t slot = uint64_t(blockIdx.x) * GZ_WARPS + warp;
     const uint32_t cap = P.cap;
-    uint8_t *const text = P.scratch + slot * P.scratch_stride;
-    uint32_t *const idx = reinterpret_cast<uint32_t *>(text + cap + 64);
+    uint8_t *const text_g = P.scratch + slot * P.scratch_stride;
+    uint32_t *const idx = reinterpret_cast<uint32_t *>(text_g + cap + 64);
     uint16_t *const occ = reinterpret_cast<uint16_t *>(idx + cap);
     uint32_t *const start = s_start;
     dsz::Trees &T = *s_trees;
@@ -172,6 +201,7 @@ __global__ void __launch_bounds__(GZ_WARPS * 32) gzip_size_kernel(const GzParams
             continue;
         }
         const uint32_t n = uint32_t(total);
+        uint8_t *const text = n + 64u <= GZ_SMEM_TEXT ? text_s : text_g;
         // 1. the uppercase dna5 string
         uint32_t at = 0;
         for (uint32_t s = seg0; s < seg1; ++s) {
@@ -243,8 +273,7 @@ __global__ void __launch_bounds__(GZ_WARPS * 32) gzip_size_kernel(const GzParams
         if (lane == 0) dsz::init_block(T);
         __syncwarp();
         WarpSink sink{T, lane};
-        WarpMatcher M{text, occ, idx, n, np, lane, 0xFFFFFF00u, 0u, 0u, {0u, 0u, 0u, 0u}, 0u};
-        M.wb = 0u - 32u;      // nothing windowed yet: wb + 32 == 0, the first window() call loads
+        WarpMatcher M{text, occ, idx, n, np, lane, 0u - 64u, 0u, 0u, {0u, 0u, 0u, 0u}, 0u, {0u, 0u, 0u, 0u}, 0u, 0xFFFFFFFFu, P.prefetch != 0};   // wb: nothing windowed yet
         const uint32_t size = dsz::gzip_size(M, sink, n);
         if (lane == 0) {
             P.size_out[r] = size;
