@@ -74,13 +74,14 @@ struct cg_handle {
     uint8_t *d_bin_to_cat = nullptr;
     uint8_t h_bin_to_cat[256];
     // model
-    bool model_set = false;
+    bool model_set = false, model_has_kde = false;
     int call_mode = 0;
     cgk::ModelDev *d_models = nullptr;
     float *d_pool = nullptr;
     cg_thresholds thr{};
     // batch buffers
     DevBuf bases, seg_off, read_seg, num_hashes, counts, unique, prob, call, conf, mq, cr, len, counter, dbg, dbgn;
+    DevBuf memo_keys, memo_vals, memo_list, memo_count, memo_slot;   // memoised model evaluation (eval_kernel.cuh), shared by the slots
     DevBuf gz_size, gz_scratch;   // compression-ratio kernel: gzip size per read (per slot), per-warp scratch (shared by the slots: their kernels never overlap)
     bool staged_device_cr = false;   // the batch came without compression ratios: gzip_size_kernel fills `cr` before the model kernels
     DevBuf seg_len, exc_pos, exc_seg_off, unpack_src;   // optional segment lengths; two-bit transport: exception list + per-segment CSR; packed input of the generic kernel
@@ -361,7 +362,24 @@ int launch_eval(cg_handle *h, uint32_t n_reads) {
     if (n_reads == 0) return 0;
     cgk::EvalParams E = make_eval(h, n_reads);
     const size_t pairs = size_t(n_reads) * h->ncat;
-    cgk::prob_kernel<<<unsigned((pairs + 127) / 128), 128, 0, h->stream>>>(E);
+    // memoised evaluation when some category is a KDE and the table (2 slots per pair, at most 2^23) stays modest
+    static const bool memo_env = [] { const char *e = std::getenv("CHARON_EVAL_MEMO"); return !e || std::atoi(e) != 0; }();
+    size_t table = 1024;
+    while (table < 2 * pairs) table <<= 1;
+    const bool memo = memo_env && h->model_has_kde && pairs >= 4096 && table <= (size_t(1) << 23);
+    if (memo) {
+        RSV(h, h->memo_keys, table * 8); RSV(h, h->memo_vals, table * 8); RSV(h, h->memo_list, pairs * 4); RSV(h, h->memo_slot, pairs * 4);
+        RSV(h, h->memo_count, 16);
+        CU(h, cudaMemsetAsync(h->memo_keys.p, 0xFF, table * 8, h->stream));
+        CU(h, cudaMemsetAsync(h->memo_count.p, 0, 4, h->stream));
+        E.memo_keys = h->memo_keys.as<unsigned long long>(); E.memo_vals = h->memo_vals.as<double>(); E.memo_list = h->memo_list.as<uint32_t>();
+        E.memo_count = h->memo_count.as<uint32_t>(); E.memo_slot = h->memo_slot.as<uint32_t>(); E.memo_mask = uint32_t(table - 1);
+        cgk::memo_prepare_kernel<<<unsigned((pairs + 127) / 128), 128, 0, h->stream>>>(E);
+        cgk::memo_unique_kernel<<<unsigned((pairs + 127) / 128), 128, 0, h->stream>>>(E);
+        h->info.last_kernel_launches += 1;
+    } else {
+        cgk::prob_kernel<<<unsigned((pairs + 127) / 128), 128, 0, h->stream>>>(E);
+    }
     cgk::call_kernel<<<(n_reads + 127) / 128, 128, 0, h->stream>>>(E);
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return fail(h, CG_ERR_CUDA, "eval kernel launch failed: %s", cudaGetErrorString(e));

@@ -41,7 +41,16 @@ struct EvalParams {
     const float *mean_quality, *compression; const uint32_t *length;
     // outputs
     double *prob; uint8_t *call; uint8_t *confidence;
+    // Memoised evaluation (memo_keys != NULL): the probability of a (read, category) pair depends only on (category,
+    // unique count, num_hashes); a batch of 131 072 reads holds ~20x fewer distinct triples than pairs, and a KDE is 500+
+    // sequential terms.  memo_prepare_kernel files every pair under its triple in an open-addressing table (the first
+    // arrival appends the slot to memo_list), memo_unique_kernel evaluates each distinct triple once, call_kernel copies the
+    // value into prob[].  Which thread arrives first does not matter: the value is a pure function of the key.
+    unsigned long long *memo_keys; double *memo_vals; uint32_t *memo_list, *memo_count, *memo_slot; uint32_t memo_mask;
 };
+constexpr unsigned long long MEMO_EMPTY = ~0ull;     // a key's top byte is the category (<= 254)
+constexpr uint32_t MEMO_NONE = 0xFFFFFFFFu;
+constexpr uint32_t MEMO_FIELD_BITS = 28;             // unique count and num_hashes each below 2^28
 
 // One KDE term: float(exp(-z^2 / 2) / sqrt(2 pi)) exactly as the reference rounds it, without libm's exp and without the
 // double division (kde_fast_exp.inc; proven identical on every float of [-15, 15] by tests/kde_exp_exhaustive.c).
@@ -101,15 +110,9 @@ __device__ __forceinline__ float dgamma_dev(float x, float shape, float scale) {
     return expf(t);
 }
 
-// one thread per (read, category): probabilities_[i] = 1.0 * Model::prob(unique_proportions_[i]).pos
-__global__ void prob_kernel(const EvalParams P) {
-    __shared__ double s_t64[64];   // 2^(j/64): per-lane indices differ, so shared memory, not the constant cache
-    if (threadIdx.x < 64) s_t64[threadIdx.x] = c_exp_t64[threadIdx.x];
-    __syncthreads();
-    const size_t idx = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
-    if (idx >= size_t(P.n_reads) * P.ncat) return;
-    const uint32_t r = uint32_t(idx / P.ncat), c = uint32_t(idx % P.ncat);
-    const float x = __fdiv_rn(float(P.unique_counts[idx]), float(P.num_hashes[r]));   // read_entry.hpp:145
+// probabilities_[i] = 1.0 * Model::prob(unique_proportions_[i]).pos for category c with the given counts
+__device__ __forceinline__ double pair_prob(const EvalParams &P, uint32_t c, uint32_t unique, uint32_t num_hashes, const double *s_t64) {
+    const float x = __fdiv_rn(float(unique), float(num_hashes));   // read_entry.hpp:145
     const ModelDev m = P.models[c];
     const float p_err = dexp300(x, P.log_rate);
     float p_pos, p_neg;
@@ -125,7 +128,57 @@ __global__ void prob_kernel(const EvalParams P) {
     }
     if (x == 1.0f) p_pos = 1.0f;
     const float total = __fadd_rn(__fadd_rn(p_err, p_pos), p_neg);
-    P.prob[idx] = double(__fdiv_rn(p_pos, total));
+    return double(__fdiv_rn(p_pos, total));
+}
+
+// one thread per (read, category)
+__global__ void prob_kernel(const EvalParams P) {
+    __shared__ double s_t64[64];   // 2^(j/64): per-lane indices differ, so shared memory, not the constant cache
+    if (threadIdx.x < 64) s_t64[threadIdx.x] = c_exp_t64[threadIdx.x];
+    __syncthreads();
+    const size_t idx = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (idx >= size_t(P.n_reads) * P.ncat) return;
+    const uint32_t r = uint32_t(idx / P.ncat), c = uint32_t(idx % P.ncat);
+    P.prob[idx] = pair_prob(P, c, P.unique_counts[idx], P.num_hashes[r], s_t64);
+}
+
+// memoised variant, step 1: one thread per (read, category).  Pairs of a KDE category are filed under their triple; the cheap
+// closed-form densities (beta, gamma) and counts beyond the key's fields are evaluated on the spot.
+__global__ void memo_prepare_kernel(const EvalParams P) {
+    __shared__ double s_t64[64];
+    if (threadIdx.x < 64) s_t64[threadIdx.x] = c_exp_t64[threadIdx.x];
+    __syncthreads();
+    const size_t idx = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (idx >= size_t(P.n_reads) * P.ncat) return;
+    const uint32_t r = uint32_t(idx / P.ncat), c = uint32_t(idx % P.ncat);
+    const uint32_t u = P.unique_counts[idx], nh = P.num_hashes[r];
+    if (P.models[c].dist != 0 || (u >> MEMO_FIELD_BITS) || (nh >> MEMO_FIELD_BITS)) {
+        P.prob[idx] = pair_prob(P, c, u, nh, s_t64);
+        P.memo_slot[idx] = MEMO_NONE;
+        return;
+    }
+    const unsigned long long key = ((unsigned long long)c << 56) | ((unsigned long long)u << MEMO_FIELD_BITS) | nh;
+    unsigned long long x = key * 0x9E3779B97F4A7C15ull;
+    uint32_t h = uint32_t(x >> 32) & P.memo_mask;
+    for (;;) {
+        const unsigned long long old = atomicCAS(&P.memo_keys[h], MEMO_EMPTY, key);
+        if (old == MEMO_EMPTY) { P.memo_list[atomicAdd(P.memo_count, 1u)] = h; break; }
+        if (old == key) break;
+        h = (h + 1u) & P.memo_mask;
+    }
+    P.memo_slot[idx] = h;
+}
+// step 2: one thread per DISTINCT triple (the grid covers the worst case; threads beyond the count leave)
+__global__ void memo_unique_kernel(const EvalParams P) {
+    __shared__ double s_t64[64];
+    if (threadIdx.x < 64) s_t64[threadIdx.x] = c_exp_t64[threadIdx.x];
+    __syncthreads();
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= *P.memo_count) return;
+    const uint32_t h = P.memo_list[t];
+    const unsigned long long key = P.memo_keys[h];
+    const uint32_t field = (1u << MEMO_FIELD_BITS) - 1u;
+    P.memo_vals[h] = pair_prob(P, uint32_t(key >> 56), uint32_t(key >> MEMO_FIELD_BITS) & field, uint32_t(key) & field, s_t64);
 }
 
 // one thread per read: call_host (mode 0) / call_category (mode 1)
@@ -133,6 +186,11 @@ __global__ void call_kernel(const EvalParams P) {
     const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
     if (r >= P.n_reads) return;
     const uint32_t nc = P.ncat;
+    if (P.memo_keys)     // step 3 of the memoised evaluation: the pair's probability is its triple's
+        for (uint32_t c = 0; c < nc; ++c) {
+            const uint32_t slot = P.memo_slot[size_t(r) * nc + c];
+            if (slot != MEMO_NONE) P.prob[size_t(r) * nc + c] = P.memo_vals[slot];
+        }
     const uint32_t *uc = P.unique_counts + size_t(r) * nc;
     const uint32_t *ct = P.counts + size_t(r) * nc;
     const double *pr = P.prob + size_t(r) * nc;

@@ -37,5 +37,11 @@ t0=$(date +%s.%N); charon_b200/charon dehost $D/reads.fq --db $D/demo.idx -t 1 -
 grep "Read loop" $D/d1.log
 else cp $D/out.tsv $D/out1.tsv; fi
 cmp $D/out.tsv $D/out1.tsv && echo "TSV identical for -t 1 and -t $T"
+# the same with the compression ratios computed on the GPU (bit-exact zlib level-6 size): the -t team no longer runs zlib
+for TT in $T 4 1; do
+t0=$(date +%s.%N); charon_b200/charon dehost $D/reads.fq --db $D/demo.idx -t $TT -v --gpu_compression --log $D/dg.log > $D/outg.tsv; t1=$(date +%s.%N); echo "charon dehost -t $TT --gpu_compression wall $(python -c "print(round($t1 - $t0, 2))") s for $N reads"
+grep "Read loop" $D/dg.log
+cmp $D/out.tsv $D/outg.tsv && echo "TSV identical with --gpu_compression (-t $TT)"
+done
 wc -l $D/out.tsv; head -2 $D/out.tsv; cut -f1,3 $D/out.tsv | sort | uniq -c
 rm -rf $D
