@@ -79,11 +79,15 @@ __device__ __forceinline__ float kde_prob(const float *__restrict__ ds, uint32_t
         while (lo < hi) { const uint32_t mid = (lo + hi) >> 1; if (kde_z(ds, mid, h, x) >= -15.0f) lo = mid + 1; else hi = mid; }
         i1 = lo;
     }
+    // Branch-free and unrolled: the terms are independent (≈25 dependent operations each), only the float additions form a
+    // chain, so four terms in flight hide most of a term's latency.  A term with |z| > 15 is exactly +0.0f; adding +0.0f
+    // leaves the running sum unchanged bit for bit (the sum starts at +0.0f and never turns into -0.0f: every term is >= +0
+    // or NaN), so "skip" and "add zero" are the same thing.  exp(NaN) = NaN poisons the sum, as in the reference.
+#pragma unroll 4
     for (uint32_t i = i0; i < i1; ++i) {
         const float z = kde_z(ds, i, h, x);
-        if (fabsf(z) > 15.0f) continue;                                 // term rounds to exactly +0.0f
-        if (z != z) { total = __fadd_rn(total, z); continue; }           // exp(NaN) = NaN poisons the sum, as in the reference
-        total = __fadd_rn(total, kde_term(z, t64));
+        const float t = kde_term(z, t64);                                // garbage outside [-15, 15] (never out of bounds): replaced below
+        total = __fadd_rn(total, fabsf(z) > 15.0f ? 0.0f : (z != z ? z : t));
     }
     return __fdiv_rn(total, __fmul_rn(h, float(n)));                    // NaN z falls through: exp(NaN) = NaN
 }
