@@ -42,7 +42,7 @@ struct EvalParams {
     // outputs
     double *prob; uint8_t *call; uint8_t *confidence;
     // Memoised evaluation (memo_keys != NULL): the probability of a (read, category) pair depends only on (category,
-    // unique count, num_hashes); a batch of 131 072 reads holds ~20x fewer distinct triples than pairs, and a KDE is 500+
+    // unique count, num_hashes); a batch of 131 072 reads holds about 3x fewer distinct triples than pairs, and a KDE is 500+
     // sequential terms.  memo_prepare_kernel files every pair under its triple in an open-addressing table (the first
     // arrival appends the slot to memo_list), memo_unique_kernel evaluates each distinct triple once, call_kernel copies the
     // value into prob[].  Which thread arrives first does not matter: the value is a pure function of the key.

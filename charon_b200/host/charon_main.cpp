@@ -160,6 +160,7 @@ public:
             for (uint64_t c : classified_counts_) n += c;
             CH_INFO(log_, "Read loop: %llu reads in %.3f s (%.0f reads/s); stage wall times: reader %.3f s, scalars + packing (-t %u) %.3f s, waiting for the GPU %.3f s, writer %.3f s",
                     n, sec, sec > 0 ? double(n) / sec : 0.0, t_reader_, unsigned(opt_.threads), t_prepare_, t_gpu_wait_, t_writer_);
+            if (prof_prep_) CH_INFO(log_, "prepare_batch, summed over threads: quality %.3f s (of which the phred sum %.3f s), packing %.3f s, freeing %.3f s", t_pq_, t_pz_, t_pp_, t_pf_);
         }
         CH_INFO(log_, "Results summary: ");
         for (size_t i = 0; i < ncat_; ++i) CH_INFO(log_, "%s :\t\t%llu", idx_.categories[i].c_str(), (unsigned long long)classified_counts_[i]);
@@ -201,6 +202,8 @@ private:
     void reader_thread(BoundedQueue<Batch> &parsed);
     void writer_thread(BoundedQueue<std::vector<ReadRow>> &done);
     void prepare_batch(Batch &b, int slot, bool allow_device_cr);
+    bool prof_prep_ = std::getenv("CHARON_PREP_PROFILE") != nullptr;
+    double t_pq_ = 0, t_pp_ = 0, t_pf_ = 0, t_pz_ = 0;
     void submit_batch(Batch &b, int slot, bool with_eval);
     void collect_batch(Batch &b, int slot, bool with_eval);
     void train_batch(Batch &b, std::vector<ReadRow> &to_print);

@@ -8,6 +8,9 @@
 // The format is sniffed from the first byte rather than from the file extension; gzip is detected by zlib.
 #pragma once
 #include <zlib.h>
+#if defined(__SSE2__)
+#include <emmintrin.h>
+#endif
 
 #include <cstdint>
 #include <cstring>
@@ -70,7 +73,7 @@ public:
                 r.qual += line_;
             }
             if (r.qual.size() != r.seq.size()) throw std::runtime_error(path_ + ": sequence and quality lengths differ in record " + r.id);
-            for (unsigned char q : r.qual) if (q < 33 || q > 126) throw std::runtime_error(path_ + ": illegal quality character in record " + r.id);
+            if (!quality_ok(r.qual)) throw std::runtime_error(path_ + ": illegal quality character in record " + r.id);
             have_line_ = read_line(line_);
         } else {
             for (;;) {
@@ -84,11 +87,47 @@ public:
     }
 
 private:
+    // Length of the leading run of plain upper-case A/C/G/T in [p, p + n), rounded down to whole vectors: those letters need
+    // neither translation nor rejection and are copied as they are (SSE2 is part of x86-64; elsewhere the run is empty and
+    // every letter goes through the table).
+    static bool quality_ok(const std::string &q) {   // phred94: every character in '!' .. '~'
+        size_t i = 0;
+        unsigned char lo = 255, hi = 0;
+#if defined(__SSE2__)
+        __m128i vlo = _mm_set1_epi8(char(0xFF)), vhi = _mm_setzero_si128();
+        for (; i + 16 <= q.size(); i += 16) {
+            const __m128i x = _mm_loadu_si128(reinterpret_cast<const __m128i *>(q.data() + i));
+            vlo = _mm_min_epu8(vlo, x); vhi = _mm_max_epu8(vhi, x);
+        }
+        alignas(16) unsigned char a[16], b[16];
+        _mm_store_si128(reinterpret_cast<__m128i *>(a), vlo); _mm_store_si128(reinterpret_cast<__m128i *>(b), vhi);
+        for (int k = 0; k < 16; ++k) { if (a[k] < lo) lo = a[k]; if (b[k] > hi) hi = b[k]; }
+#endif
+        for (; i < q.size(); ++i) { const unsigned char c = static_cast<unsigned char>(q[i]); if (c < lo) lo = c; if (c > hi) hi = c; }
+        return q.empty() || (lo >= 33 && hi <= 126);
+    }
+    static size_t plain_run(const char *p, size_t n) {
+        size_t i = 0;
+#if defined(__SSE2__)
+        const __m128i A = _mm_set1_epi8('A'), Cc = _mm_set1_epi8('C'), G = _mm_set1_epi8('G'), T = _mm_set1_epi8('T');
+        for (; i + 16 <= n; i += 16) {
+            const __m128i x = _mm_loadu_si128(reinterpret_cast<const __m128i *>(p + i));
+            const __m128i ok = _mm_or_si128(_mm_or_si128(_mm_cmpeq_epi8(x, A), _mm_cmpeq_epi8(x, Cc)), _mm_or_si128(_mm_cmpeq_epi8(x, G), _mm_cmpeq_epi8(x, T)));
+            if (_mm_movemask_epi8(ok) != 0xFFFF) break;
+        }
+#endif
+        return i;
+    }
     void append_seq(FastxRecord &r, const std::string &l) {
         const size_t o = r.seq.size();
         r.seq.resize(o + l.size());
-        size_t n = o;
-        for (unsigned char c : l) {
+        size_t n = o, i = 0;
+        while (i < l.size()) {
+            if (n == o + i) {   // nothing skipped so far: source and destination offsets agree, copy the plain run in one go
+                const size_t run = plain_run(l.data() + i, l.size() - i);
+                if (run) { std::memcpy(&r.seq[0] + n, l.data() + i, run); n += run; i += run; if (i == l.size()) break; }
+            }
+            const unsigned char c = static_cast<unsigned char>(l[i++]);
             const char m = lut_[c];
             if (!m) {
                 if (c == ' ' || c == '\t') continue;

@@ -53,6 +53,24 @@ private:
 #define CH_ERROR(lg, ...) (lg).log(0, "ERROR", __VA_ARGS__)
 #define CH_DEBUG(lg, ...) (lg).log(1, "DEBUG", __VA_ARGS__)
 
+// sum of the bytes of a string (SSE2: sixteen at a time through psadbw)
+inline uint64_t byte_sum(const std::string &q) {
+    const unsigned char *p = reinterpret_cast<const unsigned char *>(q.data());
+    const size_t n = q.size();
+    size_t i = 0;
+    uint64_t total = 0;
+#if defined(__SSE2__)
+    __m128i acc = _mm_setzero_si128();
+    const __m128i zero = _mm_setzero_si128();
+    for (; i + 16 <= n; i += 16) acc = _mm_add_epi64(acc, _mm_sad_epu8(_mm_loadu_si128(reinterpret_cast<const __m128i *>(p + i)), zero));
+    alignas(16) uint64_t lanes[2];
+    _mm_store_si128(reinterpret_cast<__m128i *>(lanes), acc);
+    total = lanes[0] + lanes[1];
+#endif
+    for (; i < n; ++i) total += p[i];
+    return total;
+}
+
 // get_compression_ratio (src/utils.cpp:114-124): gzip::compress of mapbox/gzip-hpp = zlib deflateInit2(
 // Z_DEFAULT_COMPRESSION, Z_DEFLATED, 15 + 16 (gzip wrapper), memLevel 8, Z_DEFAULT_STRATEGY), one Z_FINISH pass.
 class GzipRatio {
