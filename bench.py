@@ -257,6 +257,21 @@ def cli_tsv_check(n_reads=10_000):
             pass
         if not same:
             out["stderr_tail"] = r.stderr.decode(errors="replace")[-300:]
+        # the same run with the compression ratios computed on the GPU (--gpu_compression) and ONE host thread
+        t0 = time.time()
+        r2 = subprocess.run([exe, "dehost", os.path.join(d, "reads.fq"), "--db", os.path.join(d, "smoke.idx"), "-t", "1", "--gpu_compression",
+                             "--log", os.path.join(d, "charon2.log")], stdout=open(os.path.join(d, "gpu2.tsv"), "wb"), stderr=subprocess.PIPE, timeout=600)
+        same2 = r2.returncode == 0 and open(os.path.join(d, "gpu2.tsv"), "rb").read() == open(os.path.join(d, "oracle.tsv"), "rb").read()
+        g = {"tsv_identical_to_oracle_t1": bool(same2), "threads": 1, "charon_dehost_wall_s": round(time.time() - t0, 2)}
+        try:
+            m = re.search(r"Read loop: (\d+) reads in ([0-9.]+) s \(([0-9.]+) reads/s\)", open(os.path.join(d, "charon2.log")).read())
+            if m:
+                g.update(read_loop_s=float(m.group(2)), read_loop_reads_per_s=float(m.group(3)))
+        except Exception:
+            pass
+        if not same2:
+            g["stderr_tail"] = r2.stderr.decode(errors="replace")[-300:]
+        out["with_gpu_compression"] = g
         return out
     finally:
         shutil.rmtree(d, ignore_errors=True)
@@ -589,7 +604,8 @@ def run_b200(args, name, wl):
         if world == 1 and bad is None and not partitioned:
             gpu.sync()
             line["cli_tsv_check"] = cli_tsv_check()
-            if line["cli_tsv_check"].get("tsv_identical_to_oracle_t1") is False:
+            if line["cli_tsv_check"].get("tsv_identical_to_oracle_t1") is False or \
+                    line["cli_tsv_check"].get("with_gpu_compression", {}).get("tsv_identical_to_oracle_t1") is False:
                 bad = "the TSV of charon_b200/charon dehost differs from the oracle's on the smoke configuration: " + json.dumps(line["cli_tsv_check"])
         if bad is not None:
             sys.stderr.write(f"bench.py: PARITY FAILURE against the oracle on {n} reads of the workload: {bad}\n"
