@@ -34,6 +34,14 @@ def sequences(seed, n_random=250):
         seqs.append("".join(s))
     base = rs(3000)
     seqs += [base + base, base + base[:1500] + "N" + base[1500:], base[:100] + rs(4200) + base[:100]]      # TOO_FAR: a 3-letter match 4 kb back
+    # match-length and window limits: runs around MAX_MATCH = 258, periods 1..40 across the 32 506-letter distance limit and the
+    # 4096-letter TOO_FAR rule, Fibonacci-like letter frequencies (deep Huffman trees)
+    seqs += ["A" * n for n in (257, 258, 259, 260, 516, 517, 1000)] + ["AC" * 129 + "G", "ACGT" * 65 + "T"]
+    for period in (1, 2, 3, 5, 7, 11, 19, 40):
+        unit = rs(period)
+        seqs.append((unit * (33000 // period + 1))[:33000])
+    seqs.append(rs(5000) + "N" * 3 + rs(4090) + "NNN" + rs(100))          # a 3-letter match about 4096 back
+    seqs.append("".join(c * k for c, k in zip("ACGTN" * 4, [1, 1, 2, 3, 5, 8, 13, 21, 34, 55, 89, 144, 233, 377, 610, 987, 1597, 2584, 4181, 6765])))
     for _ in range(n_random):
         n = rng.choice([30, 200, 900, 2500, 6000, 8000, 15000])
         if rng.random() < 0.7:
@@ -94,7 +102,7 @@ def test_gpu_gzip_size_equals_zlib():
             ok = np.arange(len(seqs)) != len(seqs) - 1
             assert np.array_equal(got["ratio"][ok], ratio[ok]) and np.isnan(got["ratio"][-1])
         # paired reads: the two mates are compressed as one string (src/dehost_main.cpp:449-452)
-        pairs = seqs[30:90]
+        pairs = [s for s in seqs if len(s) <= 20_000][30:90]       # a pair longer than the kernel's limit would be flagged, not compressed
         bases2, seg_off2 = _batch_of(pairs)
         read_seg = np.arange(0, len(pairs) + 1, 2, dtype=np.uint32)
         got2 = gpu.compression_batch(bases2, seg_off2, read_seg=read_seg)
@@ -127,5 +135,25 @@ def test_classify_with_ratios_computed_on_the_device():
         common.assert_parity(got, want, prob_rtol=2e-4)
         assert gpu.info().last_gzip_kernel_ms > 0
         assert np.array_equal(gpu.fetch_compression(0, n), cr)
+    finally:
+        gpu.close()
+
+
+@pytest.mark.gpu
+def test_gpu_gzip_size_on_twenty_thousand_reads():
+    """20 000 synthetic 8 kb reads (2 % substitutions, insertions and deletions each) against zlib: every size."""
+    import charon_b200
+    from charon_b200 import api as A
+    from tests import common
+    refs = [common.synth.reference(71, 3_000_000), common.synth.reference(72, 3_000_000)]
+    gpu = charon_b200.GpuClassifier.from_references(refs, [0, 1], [0, 1], 2, device=0)
+    try:
+        n, L = 20_000, 8000
+        bases, seg_off, _ = common.fixed_length_batch(73, refs, [0.45, 0.45], n, L)
+        got = gpu.compression_batch(A.pack_batch(bases, seg_off, A.BASES_2BIT, align=64), None)
+        want = np.array([gzip_size(bytes(bases[i * L:(i + 1) * L])) for i in range(n)], np.uint32)
+        bad = np.flatnonzero(got["size"] != want)
+        assert bad.size == 0, f"{bad.size} of {n} sizes differ; first: read {bad[0]} gpu {got['size'][bad[0]]} zlib {want[bad[0]]}"
+        assert np.array_equal(got["ratio"], (want.astype(np.float64) / L).astype(np.float32))
     finally:
         gpu.close()
