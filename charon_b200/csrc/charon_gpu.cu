@@ -551,21 +551,22 @@ int launch_gzip(cg_handle *h, float *ratio_out) {
     const uint32_t n = h->staged_reads;
     if (!n) return 0;
     if (h->staged_max_read_len > dsz::DSZ_MAX_LEN)
-        return fail(h, CG_ERR_ARG, "compression ratio on the device: a read of this batch spans %llu bases, the limit is %u (zlib slides its window beyond that): "
+        return fail(h, CG_ERR_ARG, "compression ratio on the device: a read of this batch spans %llu bases, the limit is %u: "
                     "compute the ratios of this batch on the host and pass them in cg_read_scalars", (unsigned long long)h->staged_max_read_len, dsz::DSZ_MAX_LEN);
     static int blocks_per_sm = 0;
     if (!blocks_per_sm) {
-        cudaError_t e = cudaFuncSetAttribute(cgk::gzip_size_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(cgk::GZ_SMEM));
+        cudaError_t e = cudaFuncSetAttribute(cgk::gzip_size_kernel<uint16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(cgk::GZ_SMEM));
+        if (e == cudaSuccess) e = cudaFuncSetAttribute(cgk::gzip_size_kernel<uint32_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(cgk::GZ_SMEM));
         if (e != cudaSuccess) return fail(h, CG_ERR_CUDA, "gzip_size_kernel attribute: %s", cudaGetErrorString(e));
         int nb = 0;
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, cgk::gzip_size_kernel, cgk::GZ_WARPS * 32, cgk::GZ_SMEM);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, cgk::gzip_size_kernel<uint32_t>, cgk::GZ_WARPS * 32, cgk::GZ_SMEM);
         blocks_per_sm = nb > 0 ? nb : 1;
         if (const char *e = std::getenv("CHARON_GZ_BLOCKS")) { const int v = std::atoi(e); if (v >= 1 && v < blocks_per_sm) blocks_per_sm = v; }
     }
     const uint64_t cap = (std::max<uint64_t>(h->staged_max_read_len, 64) + 63) / 64 * 64;
     const uint64_t want_blocks = (uint64_t(n) + cgk::GZ_WARPS - 1) / cgk::GZ_WARPS;
     const unsigned grid = unsigned(std::min<uint64_t>(want_blocks, uint64_t(h->sm_count) * blocks_per_sm));
-    RSV(h, h->gz_scratch, size_t(grid) * cgk::GZ_WARPS * (cap * 7 + 64));
+    RSV(h, h->gz_scratch, size_t(grid) * cgk::GZ_WARPS * (cap * 9 + 64));
     RSV(h, h->gz_size, size_t(n) * 4);
     cgk::GzParams G{};
     G.bases = h->bases.as<uint8_t>(); G.format = uint32_t(h->staged_format);
@@ -573,11 +574,12 @@ int launch_gzip(cg_handle *h, float *ratio_out) {
     G.read_seg = h->staged_has_read_seg ? h->read_seg.as<uint32_t>() : nullptr;
     G.exc_pos = h->exc_pos.as<unsigned long long>(); G.exc_seg_off = h->exc_seg_off.as<uint32_t>(); G.n_exc = h->staged_n_exc;
     G.n_reads = n; G.work_counter = h->counter.as<uint32_t>();
-    G.scratch = h->gz_scratch.as<uint8_t>(); G.scratch_stride = cap * 7 + 64; G.cap = uint32_t(cap);
+    G.scratch = h->gz_scratch.as<uint8_t>(); G.scratch_stride = cap * 9 + 64; G.cap = uint32_t(cap);
     G.size_out = h->gz_size.as<uint32_t>(); G.ratio_out = ratio_out;
     { const char *e = std::getenv("CHARON_GZ_PREFETCH"); G.prefetch = e ? uint32_t(std::atoi(e)) : 0u; }   // measured: no gain (the step is a chain of dependent instructions, not a wait for memory)
     CU(h, cudaMemsetAsync(h->counter.p, 0, 4, h->stream));
-    cgk::gzip_size_kernel<<<grid, cgk::GZ_WARPS * 32, cgk::GZ_SMEM, h->stream>>>(G);
+    if (cap <= 65536) cgk::gzip_size_kernel<uint16_t><<<grid, cgk::GZ_WARPS * 32, cgk::GZ_SMEM, h->stream>>>(G);
+    else cgk::gzip_size_kernel<uint32_t><<<grid, cgk::GZ_WARPS * 32, cgk::GZ_SMEM, h->stream>>>(G);
     CU(h, cudaGetLastError());
     h->info.last_kernel_launches += 1;
     return 0;

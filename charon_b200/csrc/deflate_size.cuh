@@ -18,7 +18,11 @@
 // time.  Everything sequential (the lazy-match state machine, the trees) is written once, DS_HD, and compiled for the device
 // (gzip_size_kernel) and, for tests only, for the host (tests/deflate_size_host.cpp) where it is checked against the real
 // zlib of the box; the product never runs the host build.
-// Inputs longer than DSZ_MAX_LEN (no window slide happens up to there) are not handled: the caller gets DSZ_UNSUPPORTED.
+// Longer inputs than the 64 KB window: zlib slides the window by 32 KB whenever the lookahead runs low.  In absolute positions
+// that changes nothing for the match search (a candidate further back than MAX_DIST is refused anyway, and the slot that
+// becomes NIL after a slide is always further back than that); what it does change is that a block that began before the
+// current window base can no longer be emitted as a stored block (zlib passes buf = NULL), which gzip_size tracks.
+// Inputs longer than DSZ_MAX_LEN (16 M letters) are not handled: the caller gets DSZ_UNSUPPORTED.
 #pragma once
 #include <stdint.h>
 
@@ -44,7 +48,7 @@ constexpr int MIN_MATCH = 3, MAX_MATCH = 258, MIN_LOOKAHEAD = MAX_MATCH + MIN_MA
 constexpr uint32_t MAX_DIST = W_SIZE - MIN_LOOKAHEAD, TOO_FAR = 4096;
 constexpr uint32_t SYMS_PER_BLOCK = 16384 - 1;          // lit_bufsize - 1 with memLevel 8
 constexpr uint32_t GOOD_LENGTH = 8, MAX_LAZY = 16, NICE_LENGTH = 128, MAX_CHAIN = 128;
-constexpr uint32_t DSZ_MAX_LEN = W_SIZE + MAX_DIST - 1; // 65273: fill_window never slides the window below this
+constexpr uint32_t DSZ_MAX_LEN = (1u << 24) - 1;        // positions are kept in 24 bits (gzip_size_kernel.cuh)
 constexpr uint32_t DSZ_UNSUPPORTED = 0xFFFFFFFFu;
 constexpr int N_LETTER_CODES = 125;                      // 5^3 three-letter strings over A C G T N
 
@@ -251,7 +255,7 @@ DS_HD uint32_t letter_code(uint8_t c) { return c == 'A' ? 0u : (c == 'C' ? 1u : 
 //                                              prev_length = the value longest() would get, a hint for what to fetch
 //   uint32_t M.longest(p, prev_length, start)  zlib's longest_match at position p (start: in = previous match start, out = new)
 //   uint8_t M.at(p)                            letter at position p
-//   S.lit(c), S.dist(distance, length - 3)     _tr_tally;  uint64_t S.flush(bits, stored_len)  _tr_flush_block
+//   S.lit(c), S.dist(distance, length - 3)     _tr_tally;  uint64_t S.flush(bits, stored_len, have_buf)  _tr_flush_block
 // (on the device every lane of a warp runs this with identical values; only S decides which lane touches the trees).
 // Returns the size in bytes of the gzip stream.
 template <class M, class S>
@@ -261,8 +265,16 @@ DS_HD uint32_t gzip_size(M &m, S &sink, uint32_t n) {
     uint32_t syms = 0;
     uint32_t strstart = 0, block_start = 0, match_length = MIN_MATCH - 1, prev_length = MIN_MATCH - 1, match_start = 0, prev_match = 0;
     bool match_available = false;
+    uint32_t base = 0, filled = n < 2u * W_SIZE ? n : 2u * W_SIZE;     // window base and end of the data read into it (fill_window)
     while (strstart < n) {
-        const uint32_t lookahead = n - strstart;
+        if (filled - strstart < uint32_t(MIN_LOOKAHEAD) && filled < n) {
+            do {
+                if (strstart - base >= uint32_t(W_SIZE) + MAX_DIST) base += W_SIZE;
+                const uint32_t more = 2u * W_SIZE - (filled - base), left = n - filled;
+                filled += more < left ? more : left;
+            } while (filled - strstart < uint32_t(MIN_LOOKAHEAD) && filled < n);
+        }
+        const uint32_t lookahead = n - strstart;   // matches never reach the end of the filled window while input is left (262 > 258)
         uint32_t hash_head = 0;
         const bool has_head = lookahead >= uint32_t(MIN_MATCH) && m.head(strstart, match_length, hash_head) && hash_head != 0;
         prev_length = match_length; prev_match = match_start;
@@ -276,10 +288,10 @@ DS_HD uint32_t gzip_size(M &m, S &sink, uint32_t n) {
             strstart += prev_length - 1;          // the strings in between are inserted by construction (occ[] holds every position)
             match_available = false;
             match_length = MIN_MATCH - 1;
-            if (++syms == SYMS_PER_BLOCK) { bits = sink.flush(bits, strstart - block_start); block_start = strstart; syms = 0; }
+            if (++syms == SYMS_PER_BLOCK) { bits = sink.flush(bits, strstart - block_start, block_start >= base); block_start = strstart; syms = 0; }
         } else if (match_available) {
             sink.lit(m.at(strstart - 1));
-            if (++syms == SYMS_PER_BLOCK) { bits = sink.flush(bits, strstart - block_start); block_start = strstart; syms = 0; }
+            if (++syms == SYMS_PER_BLOCK) { bits = sink.flush(bits, strstart - block_start, block_start >= base); block_start = strstart; syms = 0; }
             strstart++;
         } else {
             match_available = true;
@@ -287,7 +299,7 @@ DS_HD uint32_t gzip_size(M &m, S &sink, uint32_t n) {
         }
     }
     if (match_available) sink.lit(m.at(strstart - 1));
-    bits = sink.flush(bits, strstart - block_start);     // the last block (Z_FINISH), also for an empty input
+    bits = sink.flush(bits, strstart - block_start, block_start >= base);     // the last block (Z_FINISH), also for an empty input
     return 10u + uint32_t((bits + 7) >> 3) + 8u;
 }
 
@@ -296,7 +308,7 @@ struct TreeSink {
     Trees &T;
     DS_HD void lit(uint8_t c) { tally_lit(T, c); }
     DS_HD void dist(uint32_t d, uint32_t lc) { tally_dist(T, d, lc); }
-    DS_HD uint64_t flush(uint64_t bits, uint32_t stored_len) { return flush_block(T, bits, stored_len, true); }
+    DS_HD uint64_t flush(uint64_t bits, uint32_t stored_len, bool have_buf) { return flush_block(T, bits, stored_len, have_buf); }
 };
 
 }  // namespace dsz

@@ -21,7 +21,7 @@ struct GzParams {
     const unsigned long long *exc_pos; const uint32_t *exc_seg_off; unsigned long long n_exc;
     uint32_t n_reads;
     uint32_t *work_counter;
-    uint8_t *scratch; uint64_t scratch_stride; uint32_t cap;   // per warp: text[cap + 64] | idx u32[cap] | occ u16[cap]; scratch_stride = 7 cap + 64
+    uint8_t *scratch; uint64_t scratch_stride; uint32_t cap;   // per warp: text[cap + 64] | idx u32[cap] | occ u16 / u32[cap]; scratch_stride = 9 cap + 64
     uint32_t prefetch;                    // fetch the predicted next position's chain candidates one step early
     uint32_t *size_out;                   // gzip size per read (DSZ_UNSUPPORTED: longer than DSZ_MAX_LEN)
     float *ratio_out;                     // float(double(size) / double(length)); may be NULL
@@ -36,9 +36,10 @@ __device__ __forceinline__ uint64_t load8(const uint8_t *text, uint32_t x) {
     return uint64_t(__funnelshift_r(w0, w1, sh)) | (uint64_t(__funnelshift_r(w1, w2, sh)) << 32);
 }
 
+template <class OccT>     // uint16_t while every position of the batch's longest read fits, else uint32_t
 struct WarpMatcher {
     const uint8_t *text;             // shared memory when the read fits there, else the warp's global scratch
-    const uint16_t *occ; const uint32_t *idx;   // idx[p] = index of p in occ[] | rank of p inside its bucket << 16
+    const OccT *occ; const uint32_t *idx;   // idx[p] = index of p in occ[] (24 bits) | min(rank of p inside its bucket, 255) << 24
     uint32_t n, np, lane;
     // register window over idx[wb .. wb + 64): lane i holds idx[wb + i] and idx[wb + 32 + i]; the upper half is fetched one
     // half ahead of its use
@@ -59,8 +60,8 @@ struct WarpMatcher {
         return d < 32u ? a : b;
     }
     __device__ __forceinline__ void fetch(uint32_t e, uint32_t (&q)[4], uint32_t &rank) const {   // up to MAX_CHAIN candidates
-        const uint32_t k = e & 0xFFFFu;
-        rank = e >> 16;
+        const uint32_t k = e & 0xFFFFFFu;
+        rank = e >> 24;                                   // saturated at 255: only min(rank, MAX_CHAIN = 128) matters
         const uint32_t m = rank < dsz::MAX_CHAIN ? rank : dsz::MAX_CHAIN;
 #pragma unroll
         for (int r = 0; r < 4; ++r) {
@@ -163,8 +164,8 @@ struct WarpSink {
     dsz::Trees &T; uint32_t lane;
     __device__ __forceinline__ void lit(uint8_t c) { if (lane == 0) dsz::tally_lit(T, c); }
     __device__ __forceinline__ void dist(uint32_t d, uint32_t lc) { if (lane == 0) dsz::tally_dist(T, d, lc); }
-    __device__ __forceinline__ uint64_t flush(uint64_t bits, uint32_t stored_len) {
-        if (lane == 0) bits = dsz::flush_block(T, bits, stored_len, true);
+    __device__ __forceinline__ uint64_t flush(uint64_t bits, uint32_t stored_len, bool have_buf) {
+        if (lane == 0) bits = dsz::flush_block(T, bits, stored_len, have_buf);
         __syncwarp();
         return __shfl_sync(0xFFFFFFFFu, bits, 0);
     }
@@ -175,6 +176,7 @@ constexpr uint32_t GZ_SMEM_TEXT = 8192 + 64;     // reads of up to 8192 letters 
 constexpr size_t GZ_WARP_SMEM = GZ_TREES_BYTES + (dsz::N_LETTER_CODES + 3) * 4 + GZ_SMEM_TEXT;
 constexpr size_t GZ_SMEM = GZ_WARPS * GZ_WARP_SMEM;
 
+template <class OccT>
 __global__ void __launch_bounds__(GZ_WARPS * 32) gzip_size_kernel(const GzParams P) {
     extern __shared__ __align__(16) unsigned char gz_smem[];
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
@@ -185,7 +187,7 @@ __global__ void __launch_bounds__(GZ_WARPS * 32) gzip_size_kernel(const GzParams
     const uint32_t cap = P.cap;
     uint8_t *const text_g = P.scratch + slot * P.scratch_stride;
     uint32_t *const idx = reinterpret_cast<uint32_t *>(text_g + cap + 64);
-    uint16_t *const occ = reinterpret_cast<uint16_t *>(idx + cap);
+    OccT *const occ = reinterpret_cast<OccT *>(idx + cap);
     uint32_t *const start = s_start;
     dsz::Trees &T = *s_trees;
     for (;;) {
@@ -265,7 +267,7 @@ __global__ void __launch_bounds__(GZ_WARPS * 32) gzip_size_kernel(const GzParams
             uint32_t basep = 0;
             if (act && lane == leader) { basep = cur[b]; cur[b] = basep + uint32_t(__popc(same)); }
             basep = __shfl_sync(0xFFFFFFFFu, basep, int(leader));
-            if (act) { const uint32_t k = basep + rank; idx[p] = k | ((k - start[b]) << 16); occ[k] = uint16_t(p); }
+            if (act) { const uint32_t k = basep + rank, rk = k - start[b]; idx[p] = k | ((rk < 255u ? rk : 255u) << 24); occ[k] = OccT(p); }
             __syncwarp();
         }
         __syncwarp();
@@ -273,7 +275,7 @@ __global__ void __launch_bounds__(GZ_WARPS * 32) gzip_size_kernel(const GzParams
         if (lane == 0) dsz::init_block(T);
         __syncwarp();
         WarpSink sink{T, lane};
-        WarpMatcher M{text, occ, idx, n, np, lane, 0u - 64u, 0u, 0u, {0u, 0u, 0u, 0u}, 0u, {0u, 0u, 0u, 0u}, 0u, 0xFFFFFFFFu, P.prefetch != 0};   // wb: nothing windowed yet
+        WarpMatcher<OccT> M{text, occ, idx, n, np, lane, 0u - 64u, 0u, 0u, {0u, 0u, 0u, 0u}, 0u, {0u, 0u, 0u, 0u}, 0u, 0xFFFFFFFFu, P.prefetch != 0};   // wb: nothing windowed yet
         const uint32_t size = dsz::gzip_size(M, sink, n);
         if (lane == 0) {
             P.size_out[r] = size;

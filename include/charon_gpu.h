@@ -230,12 +230,12 @@ int cg_eval_batch_static(cg_handle *h, uint32_t n_reads, const uint32_t *num_has
  * gzip::compress(uppercase dna5 string of the read; both mates of a pair concatenated) = zlib level 6, gzip wrapper, memLevel 8,
  * divided by the length.  The size is computed bit-exactly without writing the stream (charon_b200/csrc/deflate_size.cuh).
  * gzip_size_out[n_reads] (may be NULL): bytes; ratio_out[n_reads] (may be NULL): float(double(size) / double(length)) as the
- * reference forms it.  Reads longer than CG_GZIP_MAX_LEN bases get size 0xFFFFFFFF / ratio NaN (zlib slides its window beyond
- * that length; compute those on the host).
+ * reference forms it.  Reads longer than CG_GZIP_MAX_LEN bases (16 M: positions are kept in 24 bits) get size 0xFFFFFFFF / ratio
+ * NaN; compute those on the host.
  * The same kernel runs inside cg_classify_batch / cg_submit_batch / cg_stage_batch+cg_run_staged when
  * cg_read_scalars.compression is NULL; there a batch that holds a read longer than CG_GZIP_MAX_LEN is refused (CG_ERR_ARG),
  * and cg_fetch_compression copies the ratios of the slot's last batch back for the TSV row (after cg_wait_batch). */
-#define CG_GZIP_MAX_LEN 65273u
+#define CG_GZIP_MAX_LEN 16777215u
 int cg_compression_batch(cg_handle *h, const cg_batch *batch, uint32_t *gzip_size_out, float *ratio_out);
 int cg_fetch_compression(cg_handle *h, int slot, float *ratio_out);
 

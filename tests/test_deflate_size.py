@@ -51,7 +51,7 @@ def sequences(seed, n_random=250):
     return seqs
 
 
-LONG = [33000, 40000, 65273]       # more than 16383 symbols: several blocks; 65273 = the longest input without a window slide
+LONG = [33000, 40000, 65273, 65274, 65280, 70000, 98000, 131072, 200000]   # several blocks; beyond 65273 letters zlib slides its window (once, twice, ... five times)
 
 
 @pytest.fixture(scope="module")
@@ -65,6 +65,7 @@ def host_exe(tmp_path_factory):
 def test_restated_deflate_size_equals_zlib_on_the_host(host_exe):
     rng = random.Random(5)
     seqs = sequences(1) + ["".join(rng.choice("ACGT") for _ in range(n)) for n in LONG]
+    seqs += ["A" * 100_000, ("ACGTTGCATT" * 9000)[:88_000], "".join(rng.choice("AC") for _ in range(150_000))]     # long and repetitive: chain ranks far beyond 255
     out = subprocess.run([host_exe], input=("\n".join(seqs) + "\n").encode(), capture_output=True, check=True).stdout.decode().split()
     assert len(out) == len(seqs)
     bad = [(len(s), int(o), gzip_size(s.encode())) for s, o in zip(seqs, out) if int(o) != gzip_size(s.encode())]
@@ -87,9 +88,9 @@ def test_gpu_gzip_size_equals_zlib():
     try:
         rng = random.Random(9)
         seqs = sequences(2, n_random=400) + ["".join(rng.choice("ACGT") for _ in range(n)) for n in LONG]
-        seqs += ["acgtnACGTN" * 300, "ACGURYKM" * 500, "".join(rng.choice("ACGT") for _ in range(65274))]       # folding to dna5; one read past the limit
+        seqs += ["A" * 100_000, ("ACGTTGCATT" * 9000)[:88_000]]
+        seqs += ["acgtnACGTN" * 300, "ACGURYKM" * 500]                                                            # folding to dna5
         want = np.array([gzip_size(s.upper().translate(str.maketrans("URYKMSWBDHV", "TNNNNNNNNNN")).encode()) for s in seqs], np.uint32)
-        want[-1] = 0xFFFFFFFF
         bases, seg_off = _batch_of(seqs)
         for pack in (1, 0):
             gpu.set_host_pack(pack)
@@ -99,8 +100,7 @@ def test_gpu_gzip_size_equals_zlib():
             lens = np.array([len(s) for s in seqs], np.float64)
             with np.errstate(divide="ignore", invalid="ignore"):
                 ratio = (want.astype(np.float64) / lens).astype(np.float32)
-            ok = np.arange(len(seqs)) != len(seqs) - 1
-            assert np.array_equal(got["ratio"][ok], ratio[ok]) and np.isnan(got["ratio"][-1])
+            assert np.array_equal(got["ratio"], ratio, equal_nan=True)
         # paired reads: the two mates are compressed as one string (src/dehost_main.cpp:449-452)
         pairs = [s for s in seqs if len(s) <= 20_000][30:90]       # a pair longer than the kernel's limit would be flagged, not compressed
         bases2, seg_off2 = _batch_of(pairs)

@@ -254,7 +254,7 @@ def test_dehost_extract_trains_then_classifies(charon, small_index, tmp_path):
 def test_gpu_compression_flag_gives_the_same_bytes(charon, small_index, tmp_path):
     """--gpu_compression: the compression ratio column and every call that depends on it come from gzip_size_kernel (zlib
     level-6 gzip size, bit-exact) instead of zlib on the host threads: stdout must not change — single reads (with a tiny, an
-    empty, a low-complexity and an over-long read, whose batch falls back to the host), paired reads, and --extract."""
+    empty, a low-complexity and a 70 000-letter read, beyond zlib's 64 KB window), paired reads, and --extract."""
     idx, refs, idx_path = small_index
     reads = _mixed_reads(refs, 300, seed=15)
     reads.insert(3, ("tiny", "ACGTACG", "IIIIIII"))
@@ -262,7 +262,7 @@ def test_gpu_compression_flag_gives_the_same_bytes(charon, small_index, tmp_path
     reads.insert(20, ("polyA", "A" * 2000, "I" * 2000))
     rng = np.random.default_rng(3)
     big = "".join(rng.choice(list("ACGT"), 70_000))
-    reads.insert(150, ("too_long_for_the_kernel", big, "I" * len(big)))
+    reads.insert(150, ("longer_than_the_window", big, "I" * len(big)))
     fq = str(tmp_path / "r.fq")
     _write_fastq(fq, reads)
     want = _oracle_tsv(idx, [(r,) for r in reads], oracle.default_options(True))
