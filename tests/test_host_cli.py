@@ -49,6 +49,16 @@ def test_version_and_help(charon):
     assert "--host_unique_prop_lo_threshold" not in r.stdout and "--min_probability_diff" not in r.stdout
 
 
+def test_fastq_reader_fast_paths(tmp_path):
+    """CPU: records mixing plain runs with lower case, IUPAC codes, U and N come out as the dna5 upper-case string whatever the
+    alignment of the 16-letter fast path; a quality character outside '!' .. '~' is an error."""
+    exe = str(tmp_path / "fastx_check")
+    gxx = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else "g++"
+    subprocess.check_call([gxx, "-O2", "-std=c++14", os.path.join(ROOT, "tests", "fastx_check.cpp"), "-o", exe, "-lz"])
+    out = subprocess.run([exe, str(tmp_path / "r.fq")], capture_output=True, text=True)
+    assert out.returncode == 0 and "bad 0" in out.stdout, out.stdout + out.stderr
+
+
 def test_cli_errors(charon, tmp_path):
     fq = tmp_path / "r.fq"
     fq.write_text("@r1\nACGT\n+\nIIII\n")
