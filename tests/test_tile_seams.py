@@ -124,3 +124,56 @@ def test_two_hundred_thousand_random_reads_match_the_oracle():
             common.assert_parity(got, want)
     finally:
         gpu.close()
+
+
+@pytest.mark.gpu
+def test_full_size_batch_properties(monkeypatch):
+    """BASELINE's step size (131 072 reads x 8 kb = 1.05 G bases), where the oracle would take minutes: properties that need no
+    oracle.  The outputs of a read may depend on nothing but the read: the same rows come back when the batch is permuted,
+    cut in two, sent as ASCII or as two bits per base, and gathered by either carrier; and the first 4 096 reads agree with
+    the oracle."""
+    import charon_b200
+    from charon_b200 import api as A
+    idx, refs = common.build_oracle_index([20_000_000, 20_000_000], [0, 1], ["host", "microbial"], seed=29)
+    n, L = 131_072, 8000
+    bases, seg_off, _ = common.fixed_length_batch(78, refs, [0.45, 0.45], n, L)
+    mq, cr = common.scalars(n)
+    ln = np.full(n, L, np.uint32)
+    keys = ("num_hashes", "counts", "unique_counts", "call", "confidence")
+    results = {}
+    for carrier in ("0", "1"):
+        monkeypatch.setenv("CHARON_ASYNC_GATHER", carrier)
+        gpu = common.gpu_from_oracle(idx)
+        try:
+            gpu.set_model(charon_b200.DehostOptions(), host_index=idx.host_index)
+            gpu.set_host_pack(0)
+            whole = gpu.classify_batch(bases, seg_off, mq, cr, ln)
+            results[carrier] = whole
+            if carrier == "0":
+                continue
+            packed = gpu.classify_batch(A.pack_batch(bases, seg_off, A.BASES_2BIT, align=64), None, mq, cr, ln)
+            for k in keys:
+                assert np.array_equal(packed[k], whole[k]), ("two-bit transport", k)
+            assert np.array_equal(packed["prob"], whole["prob"], equal_nan=True)
+            # cut in two
+            h = 50_001
+            a = gpu.classify_batch(bases[: h * L], seg_off[: h + 1], mq[:h], cr[:h], ln[:h])
+            b = gpu.classify_batch(bases[h * L:], seg_off[h:] - seg_off[h], mq[h:], cr[h:], ln[h:])
+            for k in keys:
+                assert np.array_equal(np.concatenate([a[k], b[k]]), whole[k]), ("split", k)
+            # permuted
+            perm = np.random.default_rng(5).permutation(n)
+            pb = np.ascontiguousarray(bases.reshape(n, L)[perm]).reshape(-1)
+            p = gpu.classify_batch(pb, seg_off, mq, cr, ln)
+            for k in keys:
+                assert np.array_equal(p[k], whole[k][perm]), ("permutation", k)
+            assert np.array_equal(p["prob"], whole["prob"][perm], equal_nan=True)
+            # and the oracle on a slice
+            m = 4096
+            want = idx.classify_batch(bases[: m * L], seg_off[: m + 1], mean_q=mq[:m], compression=cr[:m])
+            common.assert_parity({k: v[:m] for k, v in whole.items()}, want)
+        finally:
+            gpu.close()
+    for k in keys:
+        assert np.array_equal(results["0"][k], results["1"][k]), ("gather carriers", k)
+    assert (results["1"]["call"] != 255).mean() > 0.8
