@@ -532,6 +532,10 @@ def run_b200(args, name, wl):
             traffic = json.load(open(tpath)).get(name)
         except Exception:
             traffic = None
+    # contract: `traffic` = DRAM bytes (read + write) of one launch from the ncu --set full capture, or null; the capture's
+    # description travels beside it
+    traffic_detail = traffic
+    traffic = int(traffic["bytes_for_bench_launch"]) if isinstance(traffic, dict) and "bytes_for_bench_launch" in traffic else None
     d2h = int(R * (4 + 8 * ncat + 8 * ncat + 2))
     line = {"metric": "reads_per_sec", "value": value, "unit": "reads/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ra["total_ms"] / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64",
@@ -561,7 +565,7 @@ def run_b200(args, name, wl):
             "gpu_launches": int(ra["launches"]),
             "clocks": ra["clocks"],
             "roofline": {"bound": "hbm", "kernel": "cgk::count_kernel_v3", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": traffic,
+                         "frac": achieved / peak, "traffic": traffic, "traffic_unit": "bytes per launch (dram__bytes_read.sum + dram__bytes_write.sum)", "traffic_capture": traffic_detail,
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs (burst copy)" if peaks else "fallback 6650",
                          "algorithmic_bytes_per_launch": algo_bytes, "avg_launch_ms": avg_count_ms,
                          "count_kernel_share_of_step": ra["count_ms"] / (ra["total_ms"] if world == 1 else max(ra["count_ms"] + ra["eval_ms"], 1e-9)),
