@@ -1,3 +1,6 @@
+// tools/prep_microbench.cpp — what one host thread needs per read for the phred sum, the 2-bit packing and freeing the strings (no zlib):
+// build from tools/: g++ -O2 -std=c++14 -fopenmp -o /tmp/prep_microbench prep_microbench.cpp -L../charon_b200 -lcharon_gpu -lz -Wl,-rpath,$PWD/../charon_b200
+// (3.2 us per 8 kb read on the B200 box's host; tools/prep_probe.sh times the same inside the host program)
 #include "../charon_b200/host/fastx.hpp"
 #include "../include/charon_gpu.h"
 #include <chrono>
