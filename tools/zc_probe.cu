@@ -4,7 +4,8 @@
 //   (3) gather kernel alone                            (4) ONE kernel: every warp streams its own 2 KB pieces straight from pinned
 //                                                          host memory (cp.async, one piece ahead) while it gathers
 //   (5) the streaming part of (4) alone
-//   zc_probe [filter_MB=858] [host_MB=266] [gathers_per_piece=2200] [warps_per_sm=12]
+//   build: nvcc -O3 -std=c++17 -gencode arch=compute_100a,code=sm_100a -o tools/bin/zc_probe tools/zc_probe.cu
+//   zc_probe [filter_MB=858] [host_MB=266] [gathers_per_piece=2200]   (result of round 2: profiles/zc_probe_r02.log)
 #include <cstdio>
 #include <cstdlib>
 #include <cstdint>
