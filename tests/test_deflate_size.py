@@ -157,3 +157,42 @@ def test_gpu_gzip_size_on_twenty_thousand_reads():
         assert np.array_equal(got["ratio"], (want.astype(np.float64) / L).astype(np.float32))
     finally:
         gpu.close()
+
+
+@pytest.mark.gpu
+def test_two_slots_with_device_ratios():
+    """cg_submit_batch on both slots with cg_read_scalars.compression == NULL, different batches in flight: each slot's calls equal
+    the oracle fed zlib's ratios, and cg_fetch_compression returns each slot's own ratios after its wait."""
+    import charon_b200
+    import oracle
+    from tests import common
+    idx, refs = common.build_oracle_index([300_000, 300_000], [0, 1], ["host", "microbial"], seed=47)
+    gpu = common.gpu_from_oracle(idx)
+    try:
+        gpu.set_model(charon_b200.ClassifyOptions(), host_index=0)
+        opts = oracle.default_options(dehost=False)
+        batches = []
+        for s, (n, L) in enumerate([(1500, 2500), (900, 4000), (2000, 1200)]):
+            bases, seg_off, _ = common.fixed_length_batch(80 + s, refs, [0.45, 0.45], n, L)
+            bases[: 20 * L] = np.frombuffer(((b"AC" if s else b"A") * (20 * L))[: 20 * L], np.uint8)                 # low-complexity reads
+            cr = np.array([np.float32(gzip_size(bytes(bases[i * L:(i + 1) * L])) / float(L)) for i in range(n)], np.float32)
+            mq = np.full(n, 20.0, np.float32)
+            ln = np.full(n, L, np.uint32)
+            want = idx.classify_batch(bases, seg_off, mean_q=mq, compression=cr, opts=opts)
+            batches.append((bases, seg_off, mq, ln, cr, want, n))
+        res = {}
+        for i, (bases, seg_off, mq, ln, cr, want, n) in enumerate(batches):
+            slot = i & 1
+            if i >= 2:
+                got = gpu.wait(slot)
+                j = i - 2
+                common.assert_parity(got, batches[j][5], prob_rtol=2e-4)
+                assert np.array_equal(gpu.fetch_compression(slot, batches[j][6]), batches[j][4])
+            res[slot] = gpu.submit(slot, bases, seg_off, mq, None, ln)
+        for j in (1, 2):
+            slot = j & 1
+            got = gpu.wait(slot)
+            common.assert_parity(got, batches[j][5], prob_rtol=2e-4)
+            assert np.array_equal(gpu.fetch_compression(slot, batches[j][6]), batches[j][4])
+    finally:
+        gpu.close()
