@@ -251,9 +251,9 @@ __global__ void __launch_bounds__(GZ_WARPS * 32) gzip_size_kernel(const GzParams
             if (lane == 31) start[dsz::N_LETTER_CODES] = incl;
         }
         __syncwarp();
-        // fill: chunks of 32 consecutive positions; lanes of one bucket take consecutive slots in lane (= position) order.
-        // idx doubles as the running fill count: cur[b] lives in the upper half of s_start? no — kept in occ's tail is unsafe;
-        // a second 125-entry table is cheap: reuse the Trees area (not in use before the state machine starts)
+        // fill: chunks of 32 consecutive positions; the lanes of one bucket take consecutive slots in lane (= position) order,
+        // so occ[] stays ascending inside every bucket.  The running fill counts cur[b] borrow the Trees area, which is not
+        // in use before the state machine starts.
         uint32_t *const cur = reinterpret_cast<uint32_t *>(&T);
         for (uint32_t b = lane; b < uint32_t(dsz::N_LETTER_CODES); b += 32) cur[b] = start[b];
         __syncwarp();
