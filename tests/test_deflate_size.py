@@ -196,3 +196,65 @@ def test_two_slots_with_device_ratios():
             assert np.array_equal(gpu.fetch_compression(slot, batches[j][6]), batches[j][4])
     finally:
         gpu.close()
+
+
+def structured_strings(count, seed=20260501):
+    """Strings assembled from the building blocks that steer zlib's decisions — random stretches, copies of earlier stretches
+    at every distance class (short, beyond TOO_FAR, beyond the 32 506-letter limit), runs, short periods, point changes — in
+    five alphabets from one to five letters."""
+    rng = random.Random(seed)
+    seqs = []
+    for _ in range(count):
+        letters = rng.choice(["A", "AC", "ACG", "ACGT", "ACGTN"])
+        target = rng.choice([40, 300, 2000, 9000, 9000, 40000])
+        parts, total = [], 0
+        while total < target:
+            kind = rng.random()
+            if kind < 0.35 or not parts:
+                p = "".join(rng.choice(letters) for _ in range(rng.choice([1, 2, 3, 5, 17, 60, 300, 1500])))
+            elif kind < 0.65:                                  # copy of an earlier stretch, possibly with a point change
+                src = "".join(parts)
+                ln = rng.choice([3, 4, 5, 8, 16, 40, 128, 129, 258, 259, 600])
+                st = rng.randrange(0, max(1, len(src) - ln))
+                p = list(src[st:st + ln])
+                if p and rng.random() < 0.4:
+                    p[rng.randrange(len(p))] = rng.choice(letters)
+                p = "".join(p)
+            elif kind < 0.8:
+                p = rng.choice(letters) * rng.choice([2, 3, 7, 30, 257, 258, 259, 700])
+            else:
+                unit = "".join(rng.choice(letters) for _ in range(rng.choice([2, 3, 4, 7, 13])))
+                p = unit * rng.choice([2, 5, 40, 200])
+            parts.append(p)
+            total += len(p)
+        seqs.append("".join(parts))
+    return seqs
+
+
+def test_restated_deflate_size_on_structured_random_strings(host_exe):
+    """CPU, seeded: 1 500 structured strings, every size against zlib."""
+    seqs = structured_strings(1500)
+    out = subprocess.run([host_exe], input=("\n".join(seqs) + "\n").encode(), capture_output=True, check=True).stdout.decode().split()
+    assert len(out) == len(seqs)
+    bad = [(len(s), int(o), gzip_size(s.encode())) for s, o in zip(seqs, out) if int(o) != gzip_size(s.encode())]
+    assert not bad, f"{len(bad)} of {len(seqs)} sizes differ from zlib; first (length, got, zlib): {bad[:5]}"
+
+
+@pytest.mark.gpu
+def test_gpu_gzip_size_on_structured_random_strings():
+    """The same family of strings (another seed) through cg_compression_batch, both transports."""
+    import charon_b200
+    from tests import common
+    idx, refs = common.build_oracle_index([50_000, 50_000], [0, 1], ["host", "microbial"], seed=49)
+    gpu = common.gpu_from_oracle(idx)
+    try:
+        seqs = structured_strings(1200, seed=77)
+        want = np.array([gzip_size(s.encode()) for s in seqs], np.uint32)
+        bases, seg_off = _batch_of(seqs)
+        for pack in (1, 0):
+            gpu.set_host_pack(pack)
+            got = gpu.compression_batch(bases, seg_off)
+            bad = np.flatnonzero(got["size"] != want)
+            assert bad.size == 0, f"pack {pack}: {bad.size} of {len(seqs)} differ; first: length {len(seqs[bad[0]])} gpu {got['size'][bad[0]]} zlib {want[bad[0]]}"
+    finally:
+        gpu.close()
